@@ -1,0 +1,182 @@
+/*
+ * mdt_b200.h -- C ABI of libmdt_b200.so, the sm_100a (B200) implementation of mDT's
+ * graph-transformer hot path.
+ *
+ * Conventions:
+ *   - every pointer is a DEVICE pointer unless its name ends in _host;
+ *   - the caller owns every buffer (inputs, outputs, workspaces); the library keeps no
+ *     device memory of its own;
+ *   - `stream` is a cudaStream_t passed as void*; all work is stream-ordered, nothing
+ *     synchronises the device;
+ *   - every entry returns 0 on success and a negative MDT_E* code on failure; the text
+ *     of the last failure of the calling thread is mdt_last_error_string();
+ *   - nothing throws across this boundary; there is no CPU fallback behind it.
+ *
+ * Each entry cites the reference interface (file:line under /root/reference) it replaces.
+ */
+#ifndef MDT_B200_H
+#define MDT_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MDT_ABI_VERSION 1
+
+#define MDT_OK 0
+#define MDT_EINVAL (-1)   /* bad argument (shape, alignment, dtype, range) */
+#define MDT_ECUDA (-2)    /* CUDA runtime / driver error, see mdt_last_error_string() */
+#define MDT_ENOSUP (-3)   /* valid request outside what the kernels cover */
+
+/* dtype codes for float buffers */
+#define MDT_F32 0
+#define MDT_BF16 1
+
+/* spatial_pos flavours produced by mdt_collate_graphs */
+#define MDT_SPATIAL_CANTOR 0 /* mDT: Cantor-paired (hops up, hops down), pre_processing.py:31-53 */
+#define MDT_SPATIAL_SPD 1    /* upstream Graphormer: shortest-path distance itself */
+
+/* bias-code bytes consumed by the fused attention (bias synthesised in-kernel) */
+#define MDT_CODE_VIRTUAL 254 /* graph-token virtual distance t[h], graphormer_layers.py:105-106 */
+#define MDT_CODE_MASKED 255  /* -inf */
+
+typedef void *mdt_stream_t;
+
+int mdt_abi_version(void);
+const char *mdt_last_error_string(void);
+/* 1 when the current device is sm_100 (B200); the library refuses to launch otherwise. */
+int mdt_device_ok(void);
+
+/* ------------------------------------------------------------------------------------
+ * A1  floyd_warshall                       mDT/src/data/algos.pyx:7-52
+ * Batched all-pairs shortest paths on dense adjacency matrices, bit-exact against the
+ * Cython routine: M = min(distance, 510), diagonal 0, zero entries mean "no edge".
+ *   adj        [B, n, n], elem_bytes 1 (uint8) | 4 (int32) | 8 (int64), values >= 0
+ *   M          [B, n, n] int64 out (may be NULL)
+ *   path       [B, n, n] int64 out, last strictly-improving k (algos.pyx:41-43), -1 / 510;
+ *              NULL skips the predecessor matrix (and the slower kernel that orders k
+ *              strictly); needs workspace of mdt_apsp_workspace_bytes(B, n)
+ *   n <= 512.
+ * ------------------------------------------------------------------------------------ */
+int64_t mdt_apsp_workspace_bytes(int B, int n);
+int mdt_apsp_batched(const void *adj, int elem_bytes, int B, int n, int64_t *M, int64_t *path,
+                     void *workspace, mdt_stream_t stream);
+
+/* A1b gen_edge_input                         mDT/src/data/algos.pyx:55-89
+ *   path [B,n,n] int64 (from mdt_apsp_batched), edge_feat [B,n,n,F] int64
+ *   out  [B,n,n,max_dist,F] int64, -1 filled
+ *   status [B] int32: 0, or 1 where a path was longer than max_dist (the reference raises). */
+int mdt_gen_edge_input(const int64_t *path, const int64_t *edge_feat, int B, int n, int F, int max_dist,
+                       int64_t *out, int32_t *status, mdt_stream_t stream);
+
+/* ------------------------------------------------------------------------------------
+ * A2 + A3  preprocess_item + collator (graph part)
+ *          mDT/src/data/pyg_datasets/pre_processing.py:23-69, mDT/src/data/collator.py:69-179
+ * One launch builds every padded graph tensor of a batch from raw edge lists.
+ *   edge_src/edge_dst [E_total] int32 node ids local to their graph; graph b owns
+ *                     edges [edge_offsets[b], edge_offsets[b+1])
+ *   n_nodes           [B] int32 (1 <= n_b <= N)
+ *   N                 padded node count (max over the batch), N <= 512;  T = N + 1
+ *   spatial_pos       [B,N,N] int32 out: index+1, 0 = padding          (collator.py:59-66)
+ *   attn_bias         [B,T,T] out, 0 / -inf: -inf where hop distance >= spatial_pos_max
+ *                     (collator.py:122-126) and on padded key columns (collator.py:38-47)
+ *   in_degree         [B,N] int64 out: degree+1, 0 = padding            (collator.py:8-20)
+ *   bias_code         [B,T,code_pitch] uint8 out or NULL: one byte per (query,key) for the
+ *                     fused attention: spatial_pos value, MDT_CODE_VIRTUAL on the graph-token
+ *                     row/column, MDT_CODE_MASKED where attn_bias is -inf
+ *   adj_workspace     [B,N8,N8] uint8 scratch, N8 = N rounded up to 8
+ *   The hop pairs of the reference's distance_matrix are recovered from the tree rooted at
+ *   node 0: depth = M[0,:], up = (M + d_i - d_j)/2, down = (M - d_i + d_j)/2.
+ * ------------------------------------------------------------------------------------ */
+int mdt_collate_graphs(const int32_t *edge_src, const int32_t *edge_dst, const int32_t *edge_offsets,
+                       const int32_t *n_nodes, int B, int N, int spatial_pos_max, int flavour,
+                       int32_t *spatial_pos, void *attn_bias, int bias_dtype, int64_t *in_degree,
+                       uint8_t *bias_code, int code_pitch, uint8_t *adj_workspace, mdt_stream_t stream);
+
+/* ------------------------------------------------------------------------------------
+ * A5  GraphAttnBias.forward / backward      mDT/src/modules/graphormer_layers.py:86-110
+ *   out[b,h,i,j] = 2*attn_bias[b,i,j] + (i>=1 && j>=1 ? table[spatial_pos[b,i-1,j-1], h]
+ *                                                      : virt[h])
+ *   attn_bias [B,T,T], out / grad_out [B,H,T,T] in `dtype`; table [num_spatial,H] and
+ *   virt [H] in float32 (the parameters' master copies).
+ *   backward: grad_table [num_spatial,H] f32 (row 0 = padding_idx gets no gradient),
+ *   grad_virt [H] f32; both are accumulated into (caller zeroes them).
+ * ------------------------------------------------------------------------------------ */
+int mdt_attn_bias_fwd(const void *attn_bias, const int32_t *spatial_pos, const float *table, const float *virt,
+                      int B, int H, int N, int num_spatial, int dtype, void *out, mdt_stream_t stream);
+int mdt_attn_bias_bwd(const void *grad_out, const int32_t *spatial_pos, int B, int H, int N, int num_spatial,
+                      int dtype, float *grad_table, float *grad_virt, mdt_stream_t stream);
+
+/* ------------------------------------------------------------------------------------
+ * A6  MultiheadAttention core                mDT/src/modules/multihead_attention.py:168-199
+ *   S = q k^T (+bias) (+key padding -> -inf); P = softmax_fp32(S); O = P v
+ * tcgen05 / TMEM / TMA kernel, head_dim 64, bf16 operands, fp32 accumulation and softmax.
+ *   q,k,v     bf16, element (b,t,h,c) at b*stride_b + t*stride_t + h*stride_h + c
+ *             (strides in elements, multiples of 8; q is pre-scaled by d^-0.5 as at
+ *             multihead_attention.py:137)
+ *   bias      materialised [B,H,T,T] (`bias_dtype` MDT_F32|MDT_BF16) or NULL
+ *   code      [B,T,code_pitch] uint8 + lut [H,256] f32 (bias = lut[h][code]) or NULL
+ *             (in-kernel synthesis: the [B,H,T,T] tensor never exists)
+ *   key_pad   [B,T] uint8 (non-zero = padded key) or NULL
+ *   out       bf16, same addressing as q with its own strides
+ *   lse       [B,H,T] f32 out: log-sum-exp of each row (saved for backward)
+ * backward: grad_out like out; dq/dk/dv like q/k/v with their own strides (dq must be
+ *   zero-filled f32 scratch `dq_accum` [B,H,T,64] -- it is reduced across key tiles -- and is
+ *   converted into dq); grad_bias [B,H,T,T] (`bias_dtype`) or NULL; grad_lut [H,256] f32
+ *   accumulated or NULL.
+ * ------------------------------------------------------------------------------------ */
+typedef struct mdt_attn_dims {
+    int32_t B, H, T;
+    int64_t q_stride_b, q_stride_t, q_stride_h;
+    int64_t k_stride_b, k_stride_t, k_stride_h;
+    int64_t v_stride_b, v_stride_t, v_stride_h;
+    int64_t o_stride_b, o_stride_t, o_stride_h;
+} mdt_attn_dims;
+
+int mdt_biased_attn_fwd(const void *q, const void *k, const void *v, const mdt_attn_dims *dims,
+                        const void *bias, int bias_dtype, const uint8_t *code, int code_pitch,
+                        const float *lut, const uint8_t *key_pad, void *out, float *lse, mdt_stream_t stream);
+
+int mdt_biased_attn_bwd(const void *q, const void *k, const void *v, const void *out, const void *grad_out,
+                        const float *lse, const mdt_attn_dims *dims, const void *bias, int bias_dtype,
+                        const uint8_t *code, int code_pitch, const float *lut, const uint8_t *key_pad,
+                        void *dq, void *dk, void *dv, const mdt_attn_dims *grad_dims, float *dq_accum,
+                        float *delta, void *grad_bias, float *grad_lut, mdt_stream_t stream);
+
+/* ------------------------------------------------------------------------------------
+ * A4  GraphNodeFeature.forward               mDT/src/modules/graphormer_layers.py:39-50
+ *   out[b,0,:] = graph_token; out[b,1+i,:] = x[b,i,:] + E_in[in_degree[b,i]] + E_out[out_degree[b,i]]
+ *   x [B,N,C], tables [num_degree,C], out [B,N+1,C], all `dtype`; degrees int64.
+ * backward: grad_x = grad_out[:,1:,:]; grad tables / token accumulated in f32
+ *   (index 0 = padding_idx gets no gradient).
+ * ------------------------------------------------------------------------------------ */
+int mdt_node_feature_fwd(const void *x, const int64_t *in_degree, const int64_t *out_degree, const void *w_in,
+                         const void *w_out, const void *graph_token, int B, int N, int C, int num_in,
+                         int num_out, int dtype, void *out, mdt_stream_t stream);
+int mdt_node_feature_bwd(const void *grad_out, const int64_t *in_degree, const int64_t *out_degree, int B, int N,
+                         int C, int num_in, int num_out, int dtype, void *grad_x, float *grad_w_in,
+                         float *grad_w_out, float *grad_token, mdt_stream_t stream);
+
+/* ------------------------------------------------------------------------------------
+ * K12  node-major <-> padded row moves       mDT/src/modules/multigraphormer_graph_encoder.py:363-371,425,435
+ * Replaces boolean-mask indexing (which costs a device->host sync per call) by a
+ * precomputed int32 row list.
+ *   gather : dst[r, :] = src[index[r], :]   for r < n_rows
+ *   scatter: dst[index[r], :] = src[r, :]
+ *   rows are `row_elems` elements of `dtype`, with independent row pitches (in elements).
+ * ------------------------------------------------------------------------------------ */
+int mdt_gather_rows(const void *src, int64_t src_pitch, const int32_t *index, int n_rows, int row_elems,
+                    int dtype, void *dst, int64_t dst_pitch, mdt_stream_t stream);
+int mdt_scatter_rows(const void *src, int64_t src_pitch, const int32_t *index, int n_rows, int row_elems,
+                     int dtype, void *dst, int64_t dst_pitch, mdt_stream_t stream);
+
+/* Self-test of the tcgen05 building blocks (descriptor layouts); used by tests only.
+ * out_host receives max |error| of each probe against a scalar evaluation done on the device. */
+int mdt_umma_selftest(float *result_dev /*[8]*/, mdt_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MDT_B200_H */

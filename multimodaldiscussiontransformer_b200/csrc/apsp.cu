@@ -1,0 +1,536 @@
+// Batched all-pairs shortest paths + fused preprocess/collate epilogue (sm_100a).
+//
+// Replaces   mDT/src/data/algos.pyx:7-52          floyd_warshall        (A1)
+//            mDT/src/data/algos.pyx:55-89         gen_edge_input        (A1b)
+//            mDT/src/data/pyg_datasets/pre_processing.py:23-69          (A2)
+//            mDT/src/data/collator.py:69-179 (graph tensors)            (A3)
+//
+// Layout.  One graph's distance matrix lives in REGISTERS for the whole k loop: every
+// thread owns an 8x8 tile as 8x4 packed u16x2 words (all distances are clamped to 510, so
+// a sum never exceeds 1020).  Step k needs only row k and column k, which their owners
+// publish to shared memory one step ahead (row k / column k do not change during step k:
+// M[k][k] == 0 and the test is strict).  The relaxation is the DPX instruction
+// __viaddmin_u16x2: two min-plus updates per issue slot.  Graphs larger than 256 nodes are
+// split by rows over a thread-block cluster of 2 or 4 CTAs; the row broadcast goes through
+// distributed shared memory and the per-step barrier becomes a cluster barrier.  Graphs
+// smaller than 128 nodes share a CTA (several graphs per block) so small batches still
+// fill the SMs.
+#include <cooperative_groups.h>
+
+#include "common.cuh"
+
+namespace cg = cooperative_groups;
+
+namespace mdt {
+
+constexpr int kUnreach = 510;  // algos.pyx:24-30,45-50
+
+// rank of cantor(min,max) among the 21 distinct values for hops in [0,5] (pre_processing.py:31-37)
+__constant__ uint8_t c_cantor_lut[36] = {0, 1, 2, 4,  6,  9,  1, 3,  5,  7,  10, 12, 2, 5,  8,  11, 13, 15,
+                                         4, 7, 11, 14, 16, 17, 6, 10, 13, 16, 18, 19, 9, 12, 15, 17, 19, 20};
+
+struct ApspParams {
+    // input: dense adjacency [B, n_in, n_in]
+    const void *adj;
+    int elem_bytes;
+    int B;
+    int n_in;              // logical plane size of adj and of M
+    int n8;                // 8-tiles per dimension (covers max(n_in, N))
+    const int32_t *n_nodes;  // [B] or null (then n_in)
+    int graphs_per_cta;
+    int rows_tiles_per_cta;  // n8 for cluster size 1
+    // plain APSP output
+    int64_t *M;  // [B, n_in, n_in] or null
+    // collate outputs (null = skip)
+    int N;  // padded node count of the batch
+    int spatial_pos_max;
+    int flavour;
+    int32_t *spatial_pos;  // [B,N,N]
+    void *attn_bias;       // [B,T,T]
+    int bias_dtype;
+    int64_t *in_degree;  // [B,N]
+    uint8_t *code;       // [B,T,pitch]
+    int code_pitch;
+};
+
+__device__ __forceinline__ uint32_t load_adj(const void *adj, int elem_bytes, size_t idx) {
+    long long v;
+    if (elem_bytes == 1)
+        v = reinterpret_cast<const uint8_t *>(adj)[idx];
+    else if (elem_bytes == 4)
+        v = reinterpret_cast<const int32_t *>(adj)[idx];
+    else
+        v = reinterpret_cast<const long long *>(adj)[idx];
+    return v > kUnreach ? (uint32_t)kUnreach : (uint32_t)v;
+}
+
+template <typename T> __device__ __forceinline__ void store_bias(void *base, size_t idx, bool masked) {
+    reinterpret_cast<T *>(base)[idx] = from_float<T>(masked ? neg_inf() : 0.f);
+}
+__device__ __forceinline__ void store_bias_dt(void *base, int dtype, size_t idx, bool masked) {
+    if (dtype == MDT_F32)
+        store_bias<float>(base, idx, masked);
+    else
+        store_bias<__nv_bfloat16>(base, idx, masked);
+}
+
+template <int CLUSTER> __global__ void __launch_bounds__(1024, 1) apsp_tile_kernel(const ApspParams p) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    const int n8 = p.n8;
+    const int npad = n8 * 8;
+    const int rt = p.rows_tiles_per_cta;
+    const int tpg = rt * n8;  // threads per graph in this CTA
+    const int G = p.graphs_per_cta;
+    int rank = 0;
+    if constexpr (CLUSTER > 1) rank = (int)cg::this_cluster().block_rank();
+
+    const int gl = threadIdx.x / tpg;  // graph slot within the CTA
+    const int lt = threadIdx.x - gl * tpg;
+    const int cta_graph0 = (CLUSTER > 1) ? (int)(blockIdx.x / CLUSTER) : (int)blockIdx.x * G;
+    const int b = cta_graph0 + gl;
+    const int trow_l = lt / n8;
+    const int tcol = lt - trow_l * n8;
+    const int trow = rank * rt + trow_l;
+    const bool active = (gl < G) && (b < p.B) && (trow < n8);
+
+    // shared layout per graph slot: rowbuf[2][npad] u16 | colbuf[2][rt*8] u16 | deg[rt*8] i32
+    const int slot_bytes = 2 * npad * 2 + 2 * rt * 8 * 2 + rt * 8 * 4;
+    uint8_t *slot = smem_raw + (size_t)(gl < G ? gl : 0) * slot_bytes;
+    uint16_t *rowbuf = reinterpret_cast<uint16_t *>(slot);
+    uint16_t *colbuf = rowbuf + 2 * npad;
+    int *degbuf = reinterpret_cast<int *>(colbuf + 2 * rt * 8);
+
+    for (int i = threadIdx.x; i < G * rt * 8; i += blockDim.x) {
+        int s = i / (rt * 8);
+        reinterpret_cast<int *>(smem_raw + (size_t)s * slot_bytes + 2 * npad * 2 + 2 * rt * 8 * 2)[i - s * rt * 8] = 0;
+    }
+    __syncthreads();
+
+    const int n_in = p.n_in;
+    const int nb = active ? (p.n_nodes ? p.n_nodes[b] : n_in) : 0;  // nodes of this graph
+    uint32_t m[8][4];
+    if (active) {
+        const size_t plane = (size_t)b * n_in * n_in;
+#pragma unroll
+        for (int rr = 0; rr < 8; ++rr) {
+            const int i = trow * 8 + rr;
+            int cnt = 0;
+#pragma unroll
+            for (int w = 0; w < 4; ++w) {
+                uint32_t pair = 0;
+#pragma unroll
+                for (int hf = 0; hf < 2; ++hf) {
+                    const int j = tcol * 8 + w * 2 + hf;
+                    uint32_t v = 0;
+                    if (i < n_in && j < n_in) v = load_adj(p.adj, p.elem_bytes, plane + (size_t)i * n_in + j);
+                    cnt += (v != 0);
+                    uint32_t d = (i == j) ? 0u : (v == 0 ? (uint32_t)kUnreach : v);  // algos.pyx:25-30
+                    pair |= d << (16 * hf);
+                }
+                m[rr][w] = pair;
+            }
+            if (cnt) atomicAdd(&degbuf[trow_l * 8 + rr], cnt);
+        }
+    }
+
+    // publish row kk / column kk for the step that uses them
+    auto publish = [&](int kk, int buf) {
+        if (!active) return;
+        if ((kk >> 3) == trow) {
+            const int rsel = kk & 7;
+            uint4 v = make_uint4(0, 0, 0, 0);
+#pragma unroll
+            for (int rr = 0; rr < 8; ++rr)
+                if (rr == rsel) v = make_uint4(m[rr][0], m[rr][1], m[rr][2], m[rr][3]);
+            if constexpr (CLUSTER > 1) {
+                cg::cluster_group cl = cg::this_cluster();
+#pragma unroll
+                for (int r = 0; r < CLUSTER; ++r) {
+                    uint16_t *remote = cl.map_shared_rank(rowbuf, r);
+                    *reinterpret_cast<uint4 *>(remote + buf * npad + tcol * 8) = v;
+                }
+            } else {
+                *reinterpret_cast<uint4 *>(rowbuf + buf * npad + tcol * 8) = v;
+            }
+        }
+        if ((kk >> 3) == tcol) {
+            const int csel = kk & 7;
+            uint32_t out[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                uint32_t lo = 0, hi = 0;
+#pragma unroll
+                for (int w = 0; w < 4; ++w) {
+                    if (w == (csel >> 1)) {
+                        lo = m[2 * q][w];
+                        hi = m[2 * q + 1][w];
+                    }
+                }
+                const int sh = (csel & 1) * 16;
+                out[q] = ((lo >> sh) & 0xffffu) | (((hi >> sh) & 0xffffu) << 16);
+            }
+            *reinterpret_cast<uint4 *>(colbuf + buf * rt * 8 + trow_l * 8) = make_uint4(out[0], out[1], out[2], out[3]);
+        }
+    };
+    auto barrier = [&]() {
+        if constexpr (CLUSTER > 1)
+            cg::this_cluster().sync();
+        else
+            __syncthreads();
+    };
+
+    // All graphs in a CTA (and all CTAs of a cluster) must run the same number of barriers.
+    int nk = n_in;
+    if (p.n_nodes) {
+        // padded nodes are isolated: steps k >= n_b cannot improve anything, so the loop may
+        // stop at the largest n_b handled by this CTA / cluster.
+        __shared__ int s_nk;
+        if (threadIdx.x == 0) s_nk = 0;
+        __syncthreads();
+        if (active && lt == 0) atomicMax(&s_nk, nb);
+        __syncthreads();
+        nk = s_nk;
+        if constexpr (CLUSTER > 1) nk = p.n_nodes[b < p.B ? b : 0];  // one graph per cluster
+    }
+
+    publish(0, 0);
+    barrier();
+    for (int k = 0; k < nk; ++k) {
+        const int buf = k & 1;
+        if (active) {
+            const uint4 rv = *reinterpret_cast<const uint4 *>(rowbuf + buf * npad + tcol * 8);
+            const uint4 cv = *reinterpret_cast<const uint4 *>(colbuf + buf * rt * 8 + trow_l * 8);
+            const uint32_t r[4] = {rv.x, rv.y, rv.z, rv.w};
+            const uint32_t c[4] = {cv.x, cv.y, cv.z, cv.w};
+#pragma unroll
+            for (int rr = 0; rr < 8; ++rr) {
+                const uint32_t a = (c[rr >> 1] >> ((rr & 1) * 16)) & 0xffffu;
+                const uint32_t a2 = a | (a << 16);
+#pragma unroll
+                for (int w = 0; w < 4; ++w) m[rr][w] = __viaddmin_u16x2(a2, r[w], m[rr][w]);  // algos.pyx:36-43
+            }
+        }
+        if (k + 1 < nk) publish(k + 1, buf ^ 1);
+        barrier();
+    }
+
+    // ---- epilogue -------------------------------------------------------------------
+    if (p.M && active) {
+        const size_t plane = (size_t)b * n_in * n_in;
+#pragma unroll
+        for (int rr = 0; rr < 8; ++rr) {
+            const int i = trow * 8 + rr;
+            if (i >= n_in) continue;
+#pragma unroll
+            for (int w = 0; w < 4; ++w) {
+#pragma unroll
+                for (int hf = 0; hf < 2; ++hf) {
+                    const int j = tcol * 8 + w * 2 + hf;
+                    uint32_t d = (m[rr][w] >> (16 * hf)) & 0xffffu;
+                    if (d > kUnreach) d = kUnreach;  // algos.pyx:46-50
+                    if (j < n_in) p.M[plane + (size_t)i * n_in + j] = (int64_t)d;
+                }
+            }
+        }
+    }
+    if (p.spatial_pos == nullptr && p.attn_bias == nullptr && p.in_degree == nullptr && p.code == nullptr) return;
+
+    // depth of every node = distance from the root (node 0): publish final row 0
+    publish(0, 0);
+    barrier();
+    if (!active) return;
+    const int N = p.N, T = N + 1;
+    const int spmax = p.spatial_pos_max;
+    uint32_t dj[8];
+    {
+        const uint4 rv = *reinterpret_cast<const uint4 *>(rowbuf + tcol * 8);
+        const uint32_t r[4] = {rv.x, rv.y, rv.z, rv.w};
+#pragma unroll
+        for (int q = 0; q < 8; ++q) dj[q] = (r[q >> 1] >> ((q & 1) * 16)) & 0xffffu;
+    }
+#pragma unroll
+    for (int rr = 0; rr < 8; ++rr) {
+        const int i = trow * 8 + rr;
+        if (i >= N) continue;
+        const int di = rowbuf[i];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            const int j = tcol * 8 + q;
+            if (j >= N) continue;
+            const int d = (int)((m[rr][q >> 1] >> ((q & 1) * 16)) & 0xffffu);
+            const bool real = (i < nb) && (j < nb);
+            int sp = 0;
+            if (real) {
+                if (p.flavour == MDT_SPATIAL_SPD) {
+                    sp = min(d, kUnreach) + 1;
+                } else {
+                    // hop pairs of the reference's distance_matrix (hateful_discussions.py:242-264)
+                    const int up2 = d + di - (int)dj[q], dn2 = d - di + (int)dj[q];
+                    int idx = 20;  // out of range -> mapping[cantor(5,5)], pre_processing.py:44-47
+                    if (d < kUnreach && up2 >= 0 && dn2 >= 0 && up2 <= 10 && dn2 <= 10 && !(up2 & 1)) {
+                        const int up = up2 >> 1, dn = dn2 >> 1;
+                        idx = c_cantor_lut[min(up, dn) * 6 + max(up, dn)];
+                    }
+                    sp = idx + 1;  // collator.py:59-66
+                }
+            }
+            // collator.py:122-126 (clip) and :38-47 (padding: key columns -inf, padded rows 0)
+            const bool masked = (j >= nb) || (i < nb && d >= spmax);
+            if (p.spatial_pos) p.spatial_pos[((size_t)b * N + i) * N + j] = sp;
+            if (p.attn_bias) store_bias_dt(p.attn_bias, p.bias_dtype, ((size_t)b * T + i + 1) * T + j + 1, masked);
+            if (p.code)
+                p.code[((size_t)b * T + i + 1) * p.code_pitch + j + 1] =
+                    masked ? (uint8_t)MDT_CODE_MASKED : (uint8_t)min(sp, 253);
+        }
+        if (tcol == 0) {  // graph-token column and degrees
+            if (p.attn_bias) store_bias_dt(p.attn_bias, p.bias_dtype, ((size_t)b * T + i + 1) * T, false);
+            if (p.code) p.code[((size_t)b * T + i + 1) * p.code_pitch] = MDT_CODE_VIRTUAL;
+            if (p.in_degree) p.in_degree[(size_t)b * N + i] = (i < nb) ? (int64_t)degbuf[trow_l * 8 + rr] + 1 : 0;
+        }
+        if (tcol == n8 - 1 && p.code) {
+            for (int j = T; j < p.code_pitch; ++j) p.code[((size_t)b * T + i + 1) * p.code_pitch + j] = MDT_CODE_MASKED;
+        }
+    }
+    if (trow == 0) {  // graph-token row
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            const int j = tcol * 8 + q;
+            if (j >= N) continue;
+            const bool masked = j >= nb;
+            if (p.attn_bias) store_bias_dt(p.attn_bias, p.bias_dtype, (size_t)b * T * T + j + 1, masked);
+            if (p.code) p.code[(size_t)b * T * p.code_pitch + j + 1] = masked ? MDT_CODE_MASKED : MDT_CODE_VIRTUAL;
+        }
+        if (tcol == 0) {
+            if (p.attn_bias) store_bias_dt(p.attn_bias, p.bias_dtype, (size_t)b * T * T, false);
+            if (p.code) p.code[(size_t)b * T * p.code_pitch] = MDT_CODE_VIRTUAL;
+        }
+        if (tcol == n8 - 1 && p.code)
+            for (int j = T; j < p.code_pitch; ++j) p.code[(size_t)b * T * p.code_pitch + j] = MDT_CODE_MASKED;
+    }
+}
+
+// Strictly k-ordered variant that also records the predecessor matrix (algos.pyx:41-43).
+// One CTA per graph; M and path live as u16 in a caller-provided workspace.
+__global__ void __launch_bounds__(1024, 1)
+    apsp_path_kernel(const void *adj, int elem_bytes, int n, uint16_t *ws, int64_t *M, int64_t *path) {
+    const int b = blockIdx.x;
+    const size_t plane = (size_t)b * n * n;
+    uint16_t *Mw = ws + 2 * plane;
+    uint16_t *Pw = Mw + (size_t)n * n;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+    for (int i = warp; i < n; i += nwarps)
+        for (int j = lane; j < n; j += 32) {
+            uint32_t v = load_adj(adj, elem_bytes, plane + (size_t)i * n + j);
+            Mw[i * n + j] = (uint16_t)((i == j) ? 0u : (v == 0 ? (uint32_t)kUnreach : v));
+            Pw[i * n + j] = 0xffffu;
+        }
+    __syncthreads();
+    for (int k = 0; k < n; ++k) {
+        const uint16_t *Mk = Mw + (size_t)k * n;
+        for (int i = warp; i < n; i += nwarps) {
+            const uint32_t mik = Mw[i * n + k];
+            if (mik >= (uint32_t)kUnreach) continue;  // cannot improve anything <= 510
+            for (int j = lane; j < n; j += 32) {
+                const uint32_t cost = mik + Mk[j];
+                if (Mw[i * n + j] > cost) {
+                    Mw[i * n + j] = (uint16_t)cost;
+                    Pw[i * n + j] = (uint16_t)k;
+                }
+            }
+        }
+        __syncthreads();
+    }
+    for (int i = warp; i < n; i += nwarps)
+        for (int j = lane; j < n; j += 32) {
+            const uint32_t d = Mw[i * n + j];
+            const uint32_t pk = Pw[i * n + j];
+            const bool far = d >= (uint32_t)kUnreach;
+            if (M) M[plane + (size_t)i * n + j] = far ? kUnreach : (int64_t)d;
+            if (path) path[plane + (size_t)i * n + j] = far ? kUnreach : (pk == 0xffffu ? -1 : (int64_t)pk);
+        }
+}
+
+// Skipping rows with M[i][k] >= 510 in the kernel above is exact: the reference would
+// record path[i][j] = k only when M[i][j] > M[i][k] + M[k][j] >= 510, i.e. for entries
+// whose final distance is either reset to 510 (path forced to 510) or later improved again
+// below 510 (path overwritten by that later k).
+
+__global__ void edges_to_adj_kernel(const int32_t *src, const int32_t *dst, const int32_t *offsets, int B, int n8x8,
+                                    uint8_t *adj) {
+    const int b = blockIdx.y;
+    const int e0 = offsets[b], e1 = offsets[b + 1];
+    for (int e = e0 + blockIdx.x * blockDim.x + threadIdx.x; e < e1; e += gridDim.x * blockDim.x) {
+        const int s = src[e], d = dst[e];
+        if (s >= 0 && d >= 0 && s < n8x8 && d < n8x8) adj[((size_t)b * n8x8 + s) * n8x8 + d] = 1;  // pre_processing.py:28-29
+    }
+}
+
+// gen_edge_input (algos.pyx:63-89): one thread per (b,i,j); in-order expansion of the
+// predecessor matrix with an explicit stack instead of recursion.
+__global__ void gen_edge_input_kernel(const int64_t *path, const int64_t *edge_feat, int B, int n, int F, int max_dist,
+                                      int64_t *out, int32_t *status) {
+    const size_t pair = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (pair >= (size_t)B * n * n) return;
+    const int b = (int)(pair / ((size_t)n * n));
+    const int ij = (int)(pair - (size_t)b * n * n);
+    const int i = ij / n, j = ij - i * n;
+    int64_t *o = out + pair * max_dist * F;
+    for (int t = 0; t < max_dist * F; ++t) o[t] = -1;  // algos.pyx:75
+    if (i == j) return;
+    const int64_t *P = path + (size_t)b * n * n;
+    if (P[ij] == kUnreach) return;
+    const int64_t *E = edge_feat + (size_t)b * n * n * F;
+    constexpr int kStack = 96;
+    int sa[kStack], sb[kStack];
+    int sp = 0, h = 0;
+    sa[0] = i;
+    sb[0] = j;
+    sp = 1;
+    while (sp > 0) {
+        --sp;
+        const int a = sa[sp], c = sb[sp];
+        const int64_t k = P[(size_t)a * n + c];
+        if (k < 0 || k >= n) {  // direct edge a -> c
+            if (h >= max_dist) {
+                atomicExch(&status[b], 1);
+                return;
+            }
+            for (int f = 0; f < F; ++f) o[(size_t)h * F + f] = E[((size_t)a * n + c) * F + f];
+            ++h;
+        } else {
+            if (sp + 2 > kStack) {
+                atomicExch(&status[b], 2);
+                return;
+            }
+            sa[sp] = (int)k;
+            sb[sp] = c;
+            ++sp;
+            sa[sp] = a;
+            sb[sp] = (int)k;
+            ++sp;
+        }
+    }
+}
+
+static int launch_tile_kernel(ApspParams p, int n_cover, cudaStream_t stream) {
+    const int n8 = (n_cover + 7) / 8;
+    p.n8 = n8;
+    int cluster = 1;
+    if (n8 * n8 > 1024) cluster = (n8 * ((n8 + 1) / 2) <= 1024) ? 2 : 4;
+    const int rt = (n8 + cluster - 1) / cluster;
+    MDT_REQUIRE(rt * n8 <= 1024, "graph too large for the register-resident APSP kernel: n=%d (max 512)", n_cover);
+    p.rows_tiles_per_cta = rt;
+    const int tpg = rt * n8;
+    int G = 1;
+    if (cluster == 1) {
+        G = 256 / tpg;
+        if (G < 1) G = 1;
+        const int want = (p.B + 2 * num_sms() - 1) / (2 * num_sms());  // enough graphs per CTA to leave >= 2 CTAs per SM
+        if (G > want) G = want;
+        if (G < 1) G = 1;
+    }
+    p.graphs_per_cta = G;
+    const int threads = ((G * tpg + 31) / 32) * 32;
+    const int npad = n8 * 8;
+    const size_t smem = (size_t)G * (2 * npad * 2 + 2 * rt * 8 * 2 + rt * 8 * 4);
+    cudaLaunchConfig_t cfg = {};
+    cfg.blockDim = dim3(threads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    if (cluster == 1) {
+        cfg.gridDim = dim3((p.B + G - 1) / G);
+        cfg.numAttrs = 0;
+        MDT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, apsp_tile_kernel<1>, p));
+    } else {
+        cfg.gridDim = dim3(p.B * cluster);
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = cluster;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        if (cluster == 2)
+            MDT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, apsp_tile_kernel<2>, p));
+        else
+            MDT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, apsp_tile_kernel<4>, p));
+    }
+    return MDT_OK;
+}
+
+}  // namespace mdt
+
+using namespace mdt;
+
+extern "C" int64_t mdt_apsp_workspace_bytes(int B, int n) { return (int64_t)B * n * n * 2 * (int64_t)sizeof(uint16_t); }
+
+extern "C" int mdt_apsp_batched(const void *adj, int elem_bytes, int B, int n, int64_t *M, int64_t *path,
+                                void *workspace, mdt_stream_t stream) {
+    if (int rc = require_sm100()) return rc;
+    MDT_REQUIRE(adj != nullptr, "adj is null");
+    MDT_REQUIRE(elem_bytes == 1 || elem_bytes == 4 || elem_bytes == 8, "elem_bytes must be 1, 4 or 8 (got %d)", elem_bytes);
+    MDT_REQUIRE(B >= 0 && n >= 0, "negative size");
+    MDT_REQUIRE(n <= 512, "n=%d exceeds 512", n);
+    if (B == 0 || n == 0) return MDT_OK;
+    if (path != nullptr) {
+        MDT_REQUIRE(workspace != nullptr, "path output needs a workspace of mdt_apsp_workspace_bytes()");
+        apsp_path_kernel<<<B, n >= 128 ? 1024 : 256, 0, as_stream(stream)>>>(adj, elem_bytes, n, (uint16_t *)workspace, M, path);
+        MDT_CHECK_CUDA(cudaGetLastError());
+        return MDT_OK;
+    }
+    if (M == nullptr) return MDT_OK;
+    ApspParams p = {};
+    p.adj = adj;
+    p.elem_bytes = elem_bytes;
+    p.B = B;
+    p.n_in = n;
+    p.M = M;
+    return launch_tile_kernel(p, n, as_stream(stream));
+}
+
+extern "C" int mdt_gen_edge_input(const int64_t *path, const int64_t *edge_feat, int B, int n, int F, int max_dist,
+                                  int64_t *out, int32_t *status, mdt_stream_t stream) {
+    if (int rc = require_sm100()) return rc;
+    MDT_REQUIRE(path && edge_feat && out && status, "null pointer");
+    MDT_REQUIRE(B >= 0 && n >= 0 && F >= 1 && max_dist >= 0, "bad size");
+    if (B == 0 || n == 0) return MDT_OK;
+    MDT_CHECK_CUDA(cudaMemsetAsync(status, 0, sizeof(int32_t) * B, as_stream(stream)));
+    const size_t pairs = (size_t)B * n * n;
+    gen_edge_input_kernel<<<(unsigned)((pairs + 127) / 128), 128, 0, as_stream(stream)>>>(path, edge_feat, B, n, F, max_dist,
+                                                                                       out, status);
+    MDT_CHECK_CUDA(cudaGetLastError());
+    return MDT_OK;
+}
+
+extern "C" int mdt_collate_graphs(const int32_t *edge_src, const int32_t *edge_dst, const int32_t *edge_offsets,
+                                  const int32_t *n_nodes, int B, int N, int spatial_pos_max, int flavour,
+                                  int32_t *spatial_pos, void *attn_bias, int bias_dtype, int64_t *in_degree,
+                                  uint8_t *bias_code, int code_pitch, uint8_t *adj_workspace, mdt_stream_t stream) {
+    if (int rc = require_sm100()) return rc;
+    MDT_REQUIRE(edge_src && edge_dst && edge_offsets && n_nodes && adj_workspace, "null pointer");
+    MDT_REQUIRE(B >= 1 && N >= 1 && N <= 512, "bad batch shape B=%d N=%d (N <= 512)", B, N);
+    MDT_REQUIRE(flavour == MDT_SPATIAL_CANTOR || flavour == MDT_SPATIAL_SPD, "unknown flavour %d", flavour);
+    MDT_REQUIRE(bias_dtype == MDT_F32 || bias_dtype == MDT_BF16, "unknown dtype %d", bias_dtype);
+    MDT_REQUIRE(bias_code == nullptr || code_pitch >= N + 1, "code_pitch %d < T=%d", code_pitch, N + 1);
+    const int n8x8 = ((N + 7) / 8) * 8;
+    cudaStream_t s = as_stream(stream);
+    MDT_CHECK_CUDA(cudaMemsetAsync(adj_workspace, 0, (size_t)B * n8x8 * n8x8, s));
+    edges_to_adj_kernel<<<dim3(4, B), 256, 0, s>>>(edge_src, edge_dst, edge_offsets, B, n8x8, adj_workspace);
+    MDT_CHECK_CUDA(cudaGetLastError());
+    ApspParams p = {};
+    p.adj = adj_workspace;
+    p.elem_bytes = 1;
+    p.B = B;
+    p.n_in = n8x8;
+    p.n_nodes = n_nodes;
+    p.N = N;
+    p.spatial_pos_max = spatial_pos_max;
+    p.flavour = flavour;
+    p.spatial_pos = spatial_pos;
+    p.attn_bias = attn_bias;
+    p.bias_dtype = bias_dtype;
+    p.in_degree = in_degree;
+    p.code = bias_code;
+    p.code_pitch = code_pitch;
+    return launch_tile_kernel(p, n8x8, s);
+}

@@ -1,0 +1,241 @@
+// GraphAttnBias forward / backward, materialising variant (sm_100a).
+//
+// Replaces   mDT/src/modules/graphormer_layers.py:86-110   GraphAttnBias.forward   (A5)
+//
+//   out[b,h,i,j] = 2*attn_bias[b,i,j] + (i>=1 && j>=1 ? table[spatial_pos[b,i-1,j-1]][h] : virt[h])
+//
+// HBM-bound: B*T*T*(e+4) bytes in, B*H*T*T*e bytes out.  One CTA owns a chunk of one
+// graph's [T*T] plane: it stages one BYTE per position in shared memory (spatial index,
+// 254 = graph-token row/column, 255 = -inf) plus a [H][256] value table, then streams the
+// H output planes with 16-byte stores.  T = N+1 is odd, so plane starts are only
+// element-aligned: vectors are aligned on the global address and the byte codes are read
+// with a funnel shift.  Inputs whose attn_bias holds anything but 0 / -inf (or indices
+// above 253) take the element-wise path of the same kernel.
+#include "common.cuh"
+
+namespace mdt {
+
+constexpr int kChunk = 8192;
+constexpr int kBiasThreads = 256;
+
+template <typename T> struct Vec16;
+template <> struct Vec16<float> { static constexpr int n = 4; };
+template <> struct Vec16<__nv_bfloat16> { static constexpr int n = 8; };
+
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+    __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t *>(&v);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kBiasThreads)
+    attn_bias_fwd_kernel(const T *__restrict__ ab, const int32_t *__restrict__ sp, const float *__restrict__ table,
+                         const float *__restrict__ virt, int H, int N, int num_spatial, T *__restrict__ out) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    uint8_t *code = smem;                                          // [kChunk + 16]
+    float *lut = reinterpret_cast<float *>(smem + kChunk + 16);    // [H][256]
+    const int T_ = N + 1;
+    const size_t plane = (size_t)T_ * T_;
+    const int b = blockIdx.y;
+    const size_t r0 = (size_t)blockIdx.x * kChunk;
+    const int len = (int)min((size_t)kChunk, plane - r0);
+    const T *abp = ab + (size_t)b * plane + r0;
+    const int32_t *spp = sp + (size_t)b * N * N;
+
+    int ok = 1;
+    for (int e = threadIdx.x; e < len; e += kBiasThreads) {
+        const size_t r = r0 + e;
+        const int i = (int)(r / T_), j = (int)(r - (size_t)i * T_);
+        const float a = to_float(abp[e]);
+        int c = MDT_CODE_VIRTUAL;
+        if (i >= 1 && j >= 1) {
+            c = spp[(size_t)(i - 1) * N + (j - 1)];
+            ok &= (c >= 0 && c < 254);
+        }
+        if (a == neg_inf())
+            c = MDT_CODE_MASKED;
+        else
+            ok &= (a == 0.f);
+        code[e] = (uint8_t)c;
+    }
+    for (int t = threadIdx.x; t < H * 256; t += kBiasThreads) {
+        const int h = t >> 8, c = t & 255;
+        float v = 0.f;
+        if (c == MDT_CODE_MASKED)
+            v = neg_inf();
+        else if (c == MDT_CODE_VIRTUAL)
+            v = virt[h];
+        else if (c < num_spatial)
+            v = to_float(from_float<T>(table[(size_t)c * H + h]));
+        lut[t] = v;
+    }
+    const int all_ok = __syncthreads_and(ok);
+
+    constexpr int V = Vec16<T>::n;
+    if (all_ok) {
+        for (int h = 0; h < H; ++h) {
+            const float *l = lut + h * 256;
+            const size_t e0 = ((size_t)b * H + h) * plane + r0;
+            T *o = out + e0;
+            int head = (int)((V - (e0 % V)) % V);
+            if (head > len) head = len;
+            if ((int)threadIdx.x < head) o[threadIdx.x] = from_float<T>(l[code[threadIdx.x]]);
+            const int nvec = (len - head) / V;
+            for (int v = threadIdx.x; v < nvec; v += kBiasThreads) {
+                const int e = head + v * V;
+                // V consecutive code bytes starting at byte offset e (unaligned)
+                const uint32_t *w = reinterpret_cast<const uint32_t *>(code + (e & ~3));
+                const int sh = (e & 3) * 8;
+                const uint32_t w0 = w[0], w1 = w[1];
+                const uint32_t c0 = __funnelshift_r(w0, w1, sh);
+                if constexpr (V == 4) {
+                    float4 r;
+                    r.x = l[c0 & 255];
+                    r.y = l[(c0 >> 8) & 255];
+                    r.z = l[(c0 >> 16) & 255];
+                    r.w = l[c0 >> 24];
+                    __stcs(reinterpret_cast<float4 *>(o + e), r);
+                } else {
+                    const uint32_t w2 = w[2];
+                    const uint32_t c1 = __funnelshift_r(w1, w2, sh);
+                    uint4 r;
+                    r.x = pack_bf16(l[c0 & 255], l[(c0 >> 8) & 255]);
+                    r.y = pack_bf16(l[(c0 >> 16) & 255], l[c0 >> 24]);
+                    r.z = pack_bf16(l[c1 & 255], l[(c1 >> 8) & 255]);
+                    r.w = pack_bf16(l[(c1 >> 16) & 255], l[c1 >> 24]);
+                    __stcs(reinterpret_cast<uint4 *>(o + e), r);
+                }
+            }
+            const int tail0 = head + nvec * V;
+            if ((int)threadIdx.x < len - tail0) o[tail0 + threadIdx.x] = from_float<T>(l[code[tail0 + threadIdx.x]]);
+        }
+    } else {
+        // element-wise path: arbitrary attn_bias values / indices; same rounding steps as
+        // the reference (add in the tensor dtype, then add attn_bias again, :93-108)
+        for (int h = 0; h < H; ++h) {
+            T *o = out + ((size_t)b * H + h) * plane + r0;
+            for (int e = threadIdx.x; e < len; e += kBiasThreads) {
+                const size_t r = r0 + e;
+                const int i = (int)(r / T_), j = (int)(r - (size_t)i * T_);
+                const float a = to_float(abp[e]);
+                float add;
+                if (i >= 1 && j >= 1) {
+                    const int c = spp[(size_t)(i - 1) * N + (j - 1)];
+                    add = (c >= 0 && c < num_spatial) ? to_float(from_float<T>(table[(size_t)c * H + h])) : 0.f;
+                } else {
+                    add = to_float(from_float<T>(virt[h]));
+                }
+                const float s1 = to_float(from_float<T>(a + add));
+                o[e] = from_float<T>(s1 + a);
+            }
+        }
+    }
+}
+
+// backward: grad_table[c][h] += sum of grad_out over positions with spatial index c (c != 0),
+// grad_virt[h] += sum over the graph-token row and column.  Reads grad_out once; per-thread
+// private shared-memory bins for the first 32 indices (mDT uses 1..21), global atomics above.
+template <typename T>
+__global__ void __launch_bounds__(kBiasThreads)
+    attn_bias_bwd_kernel(const T *__restrict__ go, const int32_t *__restrict__ sp, int H, int N, int num_spatial,
+                         float *__restrict__ grad_table, float *__restrict__ grad_virt) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    uint16_t *code = reinterpret_cast<uint16_t *>(smem);                              // [kChunk]
+    float *bins = reinterpret_cast<float *>(smem + kChunk * sizeof(uint16_t));        // [32][kBiasThreads]
+    const int T_ = N + 1;
+    const size_t plane = (size_t)T_ * T_;
+    const int b = blockIdx.y;
+    const size_t r0 = (size_t)blockIdx.x * kChunk;
+    const int len = (int)min((size_t)kChunk, plane - r0);
+    const int32_t *spp = sp + (size_t)b * N * N;
+    for (int e = threadIdx.x; e < len; e += kBiasThreads) {
+        const size_t r = r0 + e;
+        const int i = (int)(r / T_), j = (int)(r - (size_t)i * T_);
+        int c = 0xffff;  // virtual
+        if (i >= 1 && j >= 1) {
+            c = spp[(size_t)(i - 1) * N + (j - 1)];
+            if (c < 0 || c >= num_spatial || c >= 0xfffe) c = 0;  // treated like padding: no gradient
+        }
+        code[e] = (uint16_t)c;
+    }
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int h = 0; h < H; ++h) {
+        const T *g = go + ((size_t)b * H + h) * plane + r0;
+#pragma unroll
+        for (int c = 0; c < 32; ++c) bins[c * kBiasThreads + threadIdx.x] = 0.f;
+        float vacc = 0.f;
+        for (int e = threadIdx.x; e < len; e += kBiasThreads) {
+            const int c = code[e];
+            const float v = to_float(g[e]);
+            if (c < 32)
+                bins[c * kBiasThreads + threadIdx.x] += v;
+            else if (c == 0xffff)
+                vacc += v;
+            else
+                atomicAdd(&grad_table[(size_t)c * H + h], v);
+        }
+        __syncthreads();
+        for (int c = warp; c < 32; c += kBiasThreads / 32) {
+            float s = 0.f;
+#pragma unroll
+            for (int q = 0; q < kBiasThreads / 32; ++q) s += bins[c * kBiasThreads + q * 32 + lane];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+            if (lane == 0 && c != 0 && c < num_spatial && s != 0.f) atomicAdd(&grad_table[(size_t)c * H + h], s);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) vacc += __shfl_xor_sync(0xffffffffu, vacc, o);
+        if (lane == 0 && vacc != 0.f) atomicAdd(&grad_virt[h], vacc);
+        __syncthreads();
+    }
+}
+
+}  // namespace mdt
+
+using namespace mdt;
+
+extern "C" int mdt_attn_bias_fwd(const void *attn_bias, const int32_t *spatial_pos, const float *table, const float *virt,
+                                 int B, int H, int N, int num_spatial, int dtype, void *out, mdt_stream_t stream) {
+    if (int rc = require_sm100()) return rc;
+    MDT_REQUIRE(attn_bias && spatial_pos && table && virt && out, "null pointer");
+    MDT_REQUIRE(B >= 1 && H >= 1 && N >= 1 && num_spatial >= 1, "bad shape");
+    MDT_REQUIRE(H <= 32, "H=%d > 32 heads not supported by the bias kernel", H);
+    MDT_REQUIRE(dtype == MDT_F32 || dtype == MDT_BF16, "unknown dtype %d", dtype);
+    const size_t plane = (size_t)(N + 1) * (N + 1);
+    dim3 grid((unsigned)((plane + kChunk - 1) / kChunk), B);
+    const size_t smem = kChunk + 16 + (size_t)H * 256 * sizeof(float);
+    if (dtype == MDT_F32) {
+        MDT_CHECK_CUDA(cudaFuncSetAttribute(attn_bias_fwd_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attn_bias_fwd_kernel<float><<<grid, kBiasThreads, smem, as_stream(stream)>>>(
+            (const float *)attn_bias, spatial_pos, table, virt, H, N, num_spatial, (float *)out);
+    } else {
+        MDT_CHECK_CUDA(cudaFuncSetAttribute(attn_bias_fwd_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attn_bias_fwd_kernel<__nv_bfloat16><<<grid, kBiasThreads, smem, as_stream(stream)>>>(
+            (const __nv_bfloat16 *)attn_bias, spatial_pos, table, virt, H, N, num_spatial, (__nv_bfloat16 *)out);
+    }
+    MDT_CHECK_CUDA(cudaGetLastError());
+    return MDT_OK;
+}
+
+extern "C" int mdt_attn_bias_bwd(const void *grad_out, const int32_t *spatial_pos, int B, int H, int N, int num_spatial,
+                                 int dtype, float *grad_table, float *grad_virt, mdt_stream_t stream) {
+    if (int rc = require_sm100()) return rc;
+    MDT_REQUIRE(grad_out && spatial_pos && grad_table && grad_virt, "null pointer");
+    MDT_REQUIRE(B >= 1 && H >= 1 && N >= 1 && num_spatial >= 1, "bad shape");
+    MDT_REQUIRE(dtype == MDT_F32 || dtype == MDT_BF16, "unknown dtype %d", dtype);
+    const size_t plane = (size_t)(N + 1) * (N + 1);
+    dim3 grid((unsigned)((plane + kChunk - 1) / kChunk), B);
+    const size_t smem = kChunk * sizeof(uint16_t) + 32 * kBiasThreads * sizeof(float);
+    if (dtype == MDT_F32) {
+        MDT_CHECK_CUDA(cudaFuncSetAttribute(attn_bias_bwd_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attn_bias_bwd_kernel<float><<<grid, kBiasThreads, smem, as_stream(stream)>>>((const float *)grad_out, spatial_pos, H, N,
+                                                                                    num_spatial, grad_table, grad_virt);
+    } else {
+        MDT_CHECK_CUDA(cudaFuncSetAttribute(attn_bias_bwd_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attn_bias_bwd_kernel<__nv_bfloat16><<<grid, kBiasThreads, smem, as_stream(stream)>>>(
+            (const __nv_bfloat16 *)grad_out, spatial_pos, H, N, num_spatial, grad_table, grad_virt);
+    }
+    MDT_CHECK_CUDA(cudaGetLastError());
+    return MDT_OK;
+}

@@ -1,0 +1,138 @@
+"""Drop-in for ``mDT/src/data/collator.py`` + ``pyg_datasets/pre_processing.py`` on the B200.
+
+The reference builds ``spatial_pos`` / ``distance`` / ``attn_bias`` / ``in_degree`` per item on
+the CPU with Python ``map`` over N^2 pairs (pre_processing.py:39-56) and pads them per batch
+in Python loops (collator.py:122-164).  Here ``preprocess_item`` only keeps the raw edge list
+(dataloader workers are forked and must not touch CUDA, src/__init__.py:8) and ``collator``
+ships edge lists + token ids to the device, where ONE kernel launch (``mdt_collate_graphs``)
+produces every padded graph tensor of the batch.  Output keys, shapes and dtypes are those of
+collator.py:166-179; extra keys (``bias_code``, ``node_index``, ``n_nodes``) feed the fused
+attention and the sync-free gather/scatter.
+"""
+
+from __future__ import annotations
+
+from typing import Any, Dict, List, Sequence
+
+import numpy as np
+import torch
+
+from .. import _lib
+
+
+def _np(a) -> np.ndarray:
+    if isinstance(a, torch.Tensor):
+        return a.detach().cpu().numpy()
+    return np.asarray(a)
+
+
+def preprocess_item(item):
+    """``preprocess_item`` (pre_processing.py:23-69): nothing is computed on the host any more.
+
+    The item keeps ``edge_index`` and ``x``; the O(N^2) tensors are built on the device by
+    ``collator``.  Returned unchanged so dataset wrappers can keep calling it.
+    """
+    return item
+
+
+def collate_graph_tensors(edge_index: Sequence[Any], n_nodes: Sequence[int], spatial_pos_max: int, device,
+                          flavour: int = _lib.SPATIAL_CANTOR, bias_dtype=torch.float32, with_code: bool = True):
+    """Edge lists of B graphs -> padded ``spatial_pos``, ``attn_bias``, ``in_degree`` (+ ``bias_code``)."""
+    lib = _lib.load()
+    B = len(n_nodes)
+    N = int(max(n_nodes))
+    T = N + 1
+    srcs, dsts, offs = [], [], [0]
+    for ei in edge_index:
+        e = _np(ei).astype(np.int32, copy=False).reshape(2, -1)
+        srcs.append(e[0])
+        dsts.append(e[1])
+        offs.append(offs[-1] + e.shape[1])
+    E = offs[-1]
+    # one pinned staging buffer, one H2D copy: [src | dst | offsets | n_nodes]
+    host = torch.empty(2 * E + (B + 1) + B, dtype=torch.int32).pin_memory()
+    hv = host.numpy()
+    if E:
+        hv[:E] = np.concatenate(srcs)
+        hv[E:2 * E] = np.concatenate(dsts)
+    hv[2 * E:2 * E + B + 1] = offs
+    hv[2 * E + B + 1:] = np.asarray(n_nodes, dtype=np.int32)
+    dev = host.to(device, non_blocking=True)
+    src_d, dst_d = dev[:E], dev[E:2 * E]
+    off_d, n_d = dev[2 * E:2 * E + B + 1], dev[2 * E + B + 1:]
+    spatial_pos = torch.empty((B, N, N), dtype=torch.int32, device=device)
+    attn_bias = torch.empty((B, T, T), dtype=bias_dtype, device=device)
+    in_degree = torch.empty((B, N), dtype=torch.int64, device=device)
+    pitch = (T + 15) // 16 * 16
+    code = torch.empty((B, T, pitch), dtype=torch.uint8, device=device) if with_code else None
+    n8 = (N + 7) // 8 * 8
+    ws = torch.empty((B, n8, n8), dtype=torch.uint8, device=device)
+    with torch.cuda.device(device):
+        _lib.check(lib.mdt_collate_graphs(_lib.ptr(src_d), _lib.ptr(dst_d), _lib.ptr(off_d), _lib.ptr(n_d), B, N,
+                                          int(spatial_pos_max), flavour, _lib.ptr(spatial_pos), _lib.ptr(attn_bias),
+                                          _lib.dtype_code(bias_dtype), _lib.ptr(in_degree), _lib.ptr(code), pitch,
+                                          _lib.ptr(ws), _lib.stream()), "mdt_collate_graphs")
+    return dict(spatial_pos=spatial_pos, attn_bias=attn_bias, in_degree=in_degree, bias_code=code, n_nodes=n_d)
+
+
+def collator(items: List[Any], spatial_pos_max: int = 10, device=None) -> Dict[str, Any]:
+    """``collator(items, spatial_pos_max)`` (collator.py:69-179) producing CUDA tensors.
+
+    ``items`` carry ``idx, x{input_ids,token_type_ids,attention_mask}, edge_index,
+    x_image_index, x_images, y`` (and optionally ``y_mask``, dataset.py:210-213).
+    """
+    if device is None:
+        device = torch.device("cuda", torch.cuda.current_device())
+    items = [it for it in items if it is not None]                      # dataset.py:160,195
+    B = len(items)
+    ns = [int(_np(it.x["input_ids"]).shape[0]) for it in items]
+    N = max(ns)                                                         # collator.py:127
+    L = int(_np(items[0].x["input_ids"]).shape[1])
+    g = collate_graph_tensors([it.edge_index for it in items], ns, spatial_pos_max, device)
+
+    n_real = sum(ns)
+    # node-major text (what the encoder consumes, multigraphormer_graph_encoder.py:322-324) and
+    # the flat row index of every real node in the padded [B*N] layout
+    node_index = np.concatenate([b * N + np.arange(n, dtype=np.int64) for b, n in enumerate(ns)]).astype(np.int32)
+    text = torch.empty((3, n_real, L), dtype=torch.int64).pin_memory()
+    tv = text.numpy()
+    o = 0
+    for it, n in zip(items, ns):
+        for k, key in enumerate(("input_ids", "token_type_ids", "attention_mask")):
+            tv[k, o:o + n] = _np(it.x[key])
+        o += n
+    text_d = text.to(device, non_blocking=True)
+    idx_d = torch.from_numpy(node_index).pin_memory().to(device, non_blocking=True)
+    padded = torch.zeros((3, B * N, L), dtype=torch.int64, device=device)
+    padded.index_copy_(1, idx_d.long(), text_d)                          # collator.py:131-139
+    padded = padded.view(3, B, N, L)
+    token_mask = ~padded[0].eq(0).all(dim=2)                             # collator.py:141
+
+    imgs = [it.x_images if isinstance(it.x_images, torch.Tensor) else torch.from_numpy(_np(it.x_images)) for it in items]
+    imgs = [im for im in imgs if not bool(torch.all(im.eq(0)))]          # collator.py:144
+    x_images = torch.cat(imgs).pin_memory().to(device, non_blocking=True) if imgs else None
+    x_image_indexes = torch.from_numpy(np.concatenate([_np(it.x_image_index).reshape(-1) for it in items]).astype(bool))
+    y = torch.from_numpy(np.concatenate([_np(it.y).reshape(-1) for it in items]).astype(np.float32))
+    out = dict(
+        idx=torch.tensor([int(it.idx) for it in items], dtype=torch.int64, device=device),
+        attn_bias=g["attn_bias"],
+        spatial_pos=g["spatial_pos"],
+        in_degree=g["in_degree"],
+        out_degree=g["in_degree"],                                      # collator.py:171
+        x_token_mask=token_mask,
+        x=padded[0],
+        x_token_type_ids=padded[1],
+        x_attention_mask=padded[2],
+        x_images=x_images,
+        x_image_indexes=x_image_indexes.to(device, non_blocking=True),
+        y=y.to(device, non_blocking=True),
+        # extras for the B200 path
+        bias_code=g["bias_code"],
+        node_index=idx_d,
+        n_nodes=g["n_nodes"],
+        x_nodes=text_d,
+    )
+    if all(getattr(it, "y_mask", None) is not None for it in items):
+        ym = np.concatenate([_np(it.y_mask).reshape(-1) for it in items]).astype(bool)
+        out["y_mask"] = torch.from_numpy(ym).to(device, non_blocking=True)   # dataset.py:210-213
+    return out
