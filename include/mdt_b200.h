@@ -172,9 +172,14 @@ int mdt_gather_rows(const void *src, int64_t src_pitch, const int32_t *index, in
 int mdt_scatter_rows(const void *src, int64_t src_pitch, const int32_t *index, int n_rows, int row_elems,
                      int dtype, void *dst, int64_t dst_pitch, mdt_stream_t stream);
 
-/* Self-test of the tcgen05 building blocks (descriptor layouts); used by tests only.
- * out_host receives max |error| of each probe against a scalar evaluation done on the device. */
-int mdt_umma_selftest(float *result_dev /*[8]*/, mdt_stream_t stream);
+/* Self-test of the tcgen05 building blocks (shared-memory descriptor layouts, TMA 128-byte
+ * swizzle, TMEM read-back); called by tests/ only.  All operands bf16, row major:
+ *   d1[128,128] = a[128,64] * b[128,64]^T          (A and B K-major, both via TMA)
+ *   d2[128,64]  = p[128,128] * v[128,64]           (A K-major written by threads, B MN-major)
+ *   d3[128,64]  = at[128(K),128(M)]^T * bk[64(N),128(K)]^T   (A MN-major, B K-major)
+ * d1..d3 are f32 device buffers. */
+int mdt_umma_selftest(const void *a, const void *b, const void *p, const void *v, const void *at, const void *bk,
+                      float *d1, float *d2, float *d3, mdt_stream_t stream);
 
 #ifdef __cplusplus
 }

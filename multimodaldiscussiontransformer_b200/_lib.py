@@ -51,7 +51,7 @@ SIGNATURES = {
                                      c_void_p, c_void_p, c_void_p, c_void_p]),
     "mdt_gather_rows": (c_int, [c_void_p, c_int64, c_void_p, c_int, c_int, c_int, c_void_p, c_int64, c_void_p]),
     "mdt_scatter_rows": (c_int, [c_void_p, c_int64, c_void_p, c_int, c_int, c_int, c_void_p, c_int64, c_void_p]),
-    "mdt_umma_selftest": (c_int, [c_void_p, c_void_p]),
+    "mdt_umma_selftest": (c_int, [c_void_p] * 10),
 }
 
 

@@ -1,0 +1,175 @@
+"""``torch.autograd.Function`` wrappers over the C ABI of ``libmdt_b200.so``.
+
+PyTorch supplies device memory, streams and the autograd graph; all arithmetic of the hot
+path happens in the sm_100a kernels behind ``include/mdt_b200.h``.  Nothing here falls back
+to PyTorch operators: a missing library or a CPU tensor raises.
+"""
+
+from __future__ import annotations
+
+import ctypes
+from typing import Optional
+
+import torch
+
+from . import _lib
+
+
+def _require_cuda(*tensors) -> None:
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError("libmdt_b200 operators need CUDA tensors (there is no CPU path)")
+
+
+# ------------------------------------------------------------------------------------------
+# A5  GraphAttnBias                                   graphormer_layers.py:86-110
+# ------------------------------------------------------------------------------------------
+class _AttnBias(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, attn_bias, spatial_pos, table, virt):
+        _require_cuda(attn_bias, spatial_pos, table, virt)
+        lib = _lib.load()
+        B, T, _ = attn_bias.shape
+        N = T - 1
+        H = table.shape[1]
+        attn_bias = attn_bias.contiguous()
+        sp = spatial_pos.to(torch.int32).contiguous()
+        tab = table.detach().float().contiguous()
+        vt = virt.detach().float().contiguous().view(-1)
+        out = torch.empty((B, H, T, T), dtype=attn_bias.dtype, device=attn_bias.device)
+        with torch.cuda.device(attn_bias.device):
+            _lib.check(lib.mdt_attn_bias_fwd(_lib.ptr(attn_bias), _lib.ptr(sp), _lib.ptr(tab), _lib.ptr(vt), B, H, N,
+                                             tab.shape[0], _lib.dtype_code(attn_bias.dtype), _lib.ptr(out),
+                                             _lib.stream()), "mdt_attn_bias_fwd")
+        ctx.save_for_backward(sp)
+        ctx.meta = (B, H, N, tab.shape[0], table.dtype, virt.dtype, virt.shape)
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        (sp,) = ctx.saved_tensors
+        B, H, N, S, tdt, vdt, vshape = ctx.meta
+        lib = _lib.load()
+        go = grad_out.contiguous()
+        g_table = torch.zeros((S, H), dtype=torch.float32, device=go.device)
+        g_virt = torch.zeros((H,), dtype=torch.float32, device=go.device)
+        with torch.cuda.device(go.device):
+            _lib.check(lib.mdt_attn_bias_bwd(_lib.ptr(go), _lib.ptr(sp), B, H, N, S, _lib.dtype_code(go.dtype),
+                                             _lib.ptr(g_table), _lib.ptr(g_virt), _lib.stream()), "mdt_attn_bias_bwd")
+        return None, None, g_table.to(tdt), g_virt.to(vdt).view(vshape)
+
+
+def attn_bias(attn_bias_in: torch.Tensor, spatial_pos: torch.Tensor, table: torch.Tensor, virt: torch.Tensor):
+    """``[B,T,T]`` + ``[B,N,N]`` -> materialised ``[B,H,T,T]`` (GraphAttnBias.forward)."""
+    return _AttnBias.apply(attn_bias_in, spatial_pos, table, virt)
+
+
+# ------------------------------------------------------------------------------------------
+# A4  GraphNodeFeature                                graphormer_layers.py:39-50
+# ------------------------------------------------------------------------------------------
+class _NodeFeature(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, in_degree, out_degree, w_in, w_out, token):
+        _require_cuda(x, in_degree, out_degree, w_in, w_out, token)
+        lib = _lib.load()
+        B, N, C = x.shape
+        dt = x.dtype
+        x = x.contiguous()
+        ind = in_degree.to(torch.int64).contiguous()
+        outd = out_degree.to(torch.int64).contiguous()
+        wi, wo, tk = (w.detach().to(dt).contiguous() for w in (w_in, w_out, token))
+        out = torch.empty((B, N + 1, C), dtype=dt, device=x.device)
+        with torch.cuda.device(x.device):
+            _lib.check(lib.mdt_node_feature_fwd(_lib.ptr(x), _lib.ptr(ind), _lib.ptr(outd), _lib.ptr(wi), _lib.ptr(wo),
+                                                _lib.ptr(tk), B, N, C, wi.shape[0], wo.shape[0], _lib.dtype_code(dt),
+                                                _lib.ptr(out), _lib.stream()), "mdt_node_feature_fwd")
+        ctx.save_for_backward(ind, outd)
+        ctx.meta = (B, N, C, w_in.shape, w_out.shape, token.shape, w_in.dtype, w_out.dtype, token.dtype)
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        ind, outd = ctx.saved_tensors
+        B, N, C, s_in, s_out, s_tok, d_in, d_out, d_tok = ctx.meta
+        lib = _lib.load()
+        go = grad_out.contiguous()
+        gx = torch.empty((B, N, C), dtype=go.dtype, device=go.device) if ctx.needs_input_grad[0] else None
+        g_in = torch.zeros(s_in, dtype=torch.float32, device=go.device)
+        g_out = torch.zeros(s_out, dtype=torch.float32, device=go.device)
+        g_tok = torch.zeros((C,), dtype=torch.float32, device=go.device)
+        with torch.cuda.device(go.device):
+            _lib.check(lib.mdt_node_feature_bwd(_lib.ptr(go), _lib.ptr(ind), _lib.ptr(outd), B, N, C, s_in[0], s_out[0],
+                                                _lib.dtype_code(go.dtype), _lib.ptr(gx), _lib.ptr(g_in), _lib.ptr(g_out),
+                                                _lib.ptr(g_tok), _lib.stream()), "mdt_node_feature_bwd")
+        return gx, None, None, g_in.to(d_in), g_out.to(d_out), g_tok.to(d_tok).view(s_tok)
+
+
+def node_feature(x, in_degree, out_degree, w_in, w_out, token):
+    """``[B,N,C]`` -> ``[B,N+1,C]`` (GraphNodeFeature.forward)."""
+    return _NodeFeature.apply(x, in_degree, out_degree, w_in, w_out, token)
+
+
+# ------------------------------------------------------------------------------------------
+# K12  node-major <-> padded row moves      multigraphormer_graph_encoder.py:363-371,425,435
+# ------------------------------------------------------------------------------------------
+def _move(scatter: bool, src: torch.Tensor, index: torch.Tensor, dst: torch.Tensor) -> None:
+    lib = _lib.load()
+    _require_cuda(src, index, dst)
+    assert src.dim() == 2 and dst.dim() == 2 and src.stride(1) == 1 and dst.stride(1) == 1
+    assert index.dtype == torch.int32 and index.is_contiguous()
+    fn = lib.mdt_scatter_rows if scatter else lib.mdt_gather_rows
+    with torch.cuda.device(src.device):
+        _lib.check(fn(_lib.ptr(src), src.stride(0), _lib.ptr(index), index.numel(), src.shape[1],
+                      _lib.dtype_code(src.dtype), _lib.ptr(dst), dst.stride(0), _lib.stream()),
+                   "mdt_scatter_rows" if scatter else "mdt_gather_rows")
+
+
+class _GatherRows(torch.autograd.Function):
+    """``out[r] = src[index[r]]``; ``index`` holds distinct rows."""
+
+    @staticmethod
+    def forward(ctx, src, index):
+        out = torch.empty((index.numel(), src.shape[1]), dtype=src.dtype, device=src.device)
+        _move(False, src, index, out)
+        ctx.save_for_backward(index)
+        ctx.rows = src.shape[0]
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        (index,) = ctx.saved_tensors
+        g = torch.zeros((ctx.rows, grad_out.shape[1]), dtype=grad_out.dtype, device=grad_out.device)
+        _move(True, grad_out.contiguous(), index, g)
+        return g, None
+
+
+class _ScatterRows(torch.autograd.Function):
+    """``out = base.clone(); out[index[r]] = src[r]`` (rows of ``base`` that are overwritten get no gradient)."""
+
+    @staticmethod
+    def forward(ctx, base, src, index):
+        out = base.clone()
+        _move(True, src.contiguous(), index, out)
+        ctx.save_for_backward(index)
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        (index,) = ctx.saved_tensors
+        go = grad_out.contiguous()
+        g_src = torch.empty((index.numel(), go.shape[1]), dtype=go.dtype, device=go.device)
+        _move(False, go, index, g_src)
+        g_base = None
+        if ctx.needs_input_grad[0]:
+            g_base = go.clone()
+            zeros = torch.zeros_like(g_src)
+            _move(True, zeros, index, g_base)
+        return g_base, g_src, None
+
+
+def gather_rows(src: torch.Tensor, index: torch.Tensor) -> torch.Tensor:
+    return _GatherRows.apply(src, index)
+
+
+def scatter_rows(base: torch.Tensor, src: torch.Tensor, index: torch.Tensor) -> torch.Tensor:
+    return _ScatterRows.apply(base, src, index)
