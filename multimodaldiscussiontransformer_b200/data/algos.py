@@ -39,6 +39,8 @@ def floyd_warshall_batched(adj: torch.Tensor, need_path: bool = False):
     a, eb = _adj_tensor(adj)
     M = torch.empty((B, n, n), dtype=torch.int64, device=adj.device)
     path = ws = None
+    if B == 0 or n == 0:  # nothing to launch (data_ptr() of an empty tensor is NULL)
+        return M, (torch.empty_like(M) if need_path else None)
     if need_path:
         path = torch.empty_like(M)
         ws = torch.empty(max(1, lib.mdt_apsp_workspace_bytes(B, n)), dtype=torch.uint8, device=adj.device)
