@@ -1,0 +1,50 @@
+// Shared pieces of the biased-attention kernels (A6, multihead_attention.py:168-199):
+// argument validation, the 4-D TMA maps over strided [b, t, h, 64] bf16 tensors and the
+// bias-source modes.
+#pragma once
+#include "umma.cuh"
+
+namespace mdt {
+namespace attn {
+
+constexpr int kD = 64;       // head dim (embed 768 / 12 heads)
+constexpr int kTile = 128;   // queries per CTA tile == keys per tile == UMMA M
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2 = 0.6931471805599453f;
+
+// where the additive bias of S comes from
+enum BiasMode : int {
+    kBiasNone = 0,
+    kBiasF32 = 1,   // materialised [B,H,T,T] float32
+    kBiasBF16 = 2,  // materialised [B,H,T,T] bfloat16
+    kBiasCode = 3,  // one byte per (b,q,k) + lut[H,256]: the [B,H,T,T] tensor never exists
+};
+
+inline int bias_mode(const void *bias, int bias_dtype, const uint8_t *code) {
+    if (code) return kBiasCode;
+    if (!bias) return kBiasNone;
+    return bias_dtype == MDT_F32 ? kBiasF32 : kBiasBF16;
+}
+
+// TMA view of a strided bf16 tensor addressed (b, t, h, c): dims innermost-first {64, T, H, B},
+// box {64, rows, 1, 1}, 128-byte swizzle.  Rows past T read as zeros.
+inline int make_bthd_map(CUtensorMap *map, const void *base, int B, int H, int T, int64_t sb, int64_t st, int64_t sh,
+                         int box_rows) {
+    MDT_REQUIRE(sb % 8 == 0 && st % 8 == 0 && sh % 8 == 0, "q/k/v/o strides must be multiples of 8 elements");
+    const uint64_t dims[4] = {(uint64_t)kD, (uint64_t)T, (uint64_t)H, (uint64_t)B};
+    // a dimension of extent 1 still needs a legal (multiple of 16, non-zero) stride
+    const uint64_t strides[4] = {2, (uint64_t)(st > 0 ? st : kD) * 2, (uint64_t)(sh > 0 ? sh : kD) * 2,
+                                 (uint64_t)(sb > 0 ? sb : kD) * 2};
+    const uint32_t box[4] = {(uint32_t)kD, (uint32_t)box_rows, 1, 1};
+    return make_tensor_map_bf16(map, base, 4, dims, strides, box);
+}
+
+inline int check_dims(const mdt_attn_dims *d, const char *who) {
+    MDT_REQUIRE(d != nullptr, "%s: dims is null", who);
+    MDT_REQUIRE(d->B >= 1 && d->H >= 1 && d->T >= 1, "%s: B, H, T must be >= 1 (got %d, %d, %d)", who, d->B, d->H, d->T);
+    MDT_REQUIRE(d->T <= 65535 && d->H <= 65535 && d->B <= 65535, "%s: B, H, T must fit a CUDA grid dimension", who);
+    return MDT_OK;
+}
+
+}  // namespace attn
+}  // namespace mdt

@@ -173,3 +173,109 @@ def gather_rows(src: torch.Tensor, index: torch.Tensor) -> torch.Tensor:
 
 def scatter_rows(base: torch.Tensor, src: torch.Tensor, index: torch.Tensor) -> torch.Tensor:
     return _ScatterRows.apply(base, src, index)
+
+
+# ------------------------------------------------------------------------------------------
+# A6  biased attention core (tcgen05 / TMEM / TMA)        multihead_attention.py:168-199
+# ------------------------------------------------------------------------------------------
+def _attn_dims(q, k, v, o) -> "_lib.AttnDims":
+    d = _lib.AttnDims()
+    d.B, d.T, d.H = q.shape[0], q.shape[1], q.shape[2]
+    for name, t in (("q", q), ("k", k), ("v", v), ("o", o)):
+        setattr(d, f"{name}_stride_b", t.stride(0))
+        setattr(d, f"{name}_stride_t", t.stride(1))
+        setattr(d, f"{name}_stride_h", t.stride(2))
+    return d
+
+
+def _check_bthd(name: str, t: torch.Tensor) -> torch.Tensor:
+    if t.dtype != torch.bfloat16:
+        raise TypeError(f"{name} must be bfloat16 (the tcgen05 kernel computes in bf16 with fp32 accumulation)")
+    if t.dim() != 4 or t.shape[-1] != 64:
+        raise ValueError(f"{name} must be [B, T, H, 64], got {tuple(t.shape)}")
+    ok = t.stride(3) == 1 and all(s % 8 == 0 for s in t.stride()[:3]) and t.data_ptr() % 16 == 0
+    return t if ok else t.contiguous()
+
+
+def _empty_like_layout(q: torch.Tensor) -> torch.Tensor:
+    """Output buffer [B,T,H,64] whose memory order follows q's (t-major for the encoder's [T,B,C] activations)."""
+    B, T, H, D = q.shape
+    if q.stride(1) > q.stride(0):
+        return torch.empty((T, B, H, D), dtype=q.dtype, device=q.device).permute(1, 0, 2, 3)
+    return torch.empty((B, T, H, D), dtype=q.dtype, device=q.device)
+
+
+class _BiasedAttention(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, q, k, v, bias, code, lut, key_pad):
+        _require_cuda(q, k, v, bias, code, lut, key_pad)
+        lib = _lib.load()
+        q, k, v = _check_bthd("q", q), _check_bthd("k", k), _check_bthd("v", v)
+        B, T, H, _ = q.shape
+        if bias is not None:
+            if bias.shape != (B, H, T, T):
+                raise ValueError(f"bias must be [B,H,T,T]={B, H, T, T}, got {tuple(bias.shape)}")
+            bias = bias.contiguous()
+        pitch = 0
+        if code is not None:
+            if code.dtype != torch.uint8 or code.dim() != 3 or code.shape[0] != B or code.shape[1] != T:
+                raise ValueError("code must be uint8 [B, T, pitch]")
+            code = code.contiguous()
+            pitch = code.shape[2]
+            lut = lut.detach().float().contiguous()
+            if lut.shape != (H, 256):
+                raise ValueError("lut must be [H, 256]")
+        if key_pad is not None:
+            key_pad = key_pad.to(torch.uint8).contiguous()
+        out = _empty_like_layout(q)
+        lse = torch.empty((B, H, T), dtype=torch.float32, device=q.device)
+        dims = _attn_dims(q, k, v, out)
+        with torch.cuda.device(q.device):
+            _lib.check(lib.mdt_biased_attn_fwd(_lib.ptr(q), _lib.ptr(k), _lib.ptr(v), ctypes.byref(dims), _lib.ptr(bias),
+                                               _lib.dtype_code(bias.dtype) if bias is not None else 0, _lib.ptr(code),
+                                               pitch, _lib.ptr(lut) if code is not None else None, _lib.ptr(key_pad),
+                                               _lib.ptr(out), _lib.ptr(lse), _lib.stream()), "mdt_biased_attn_fwd")
+        ctx.save_for_backward(q, k, v, out, lse, bias, code, lut if code is not None else None, key_pad)
+        ctx.pitch = pitch
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        q, k, v, out, lse, bias, code, lut, key_pad = ctx.saved_tensors
+        lib = _lib.load()
+        B, T, H, _ = q.shape
+        go = _check_bthd("grad_out", grad_out)
+        dq, dk, dv = _empty_like_layout(q), _empty_like_layout(q), _empty_like_layout(q)
+        dq_accum = torch.zeros((B, H, T, 64), dtype=torch.float32, device=q.device)
+        delta = torch.empty((B, H, T), dtype=torch.float32, device=q.device)
+        g_bias = torch.empty_like(bias) if (bias is not None and ctx.needs_input_grad[3]) else None
+        g_lut = torch.zeros((H, 256), dtype=torch.float32, device=q.device) if (
+            code is not None and ctx.needs_input_grad[5]) else None
+        dims = _attn_dims(q, k, v, out)
+        # grad_out is addressed through the "o" strides of gdims; dq/dk/dv through q/k/v strides of gdims
+        gdims = _attn_dims(dq, dk, dv, go)
+        with torch.cuda.device(q.device):
+            _lib.check(lib.mdt_biased_attn_bwd(
+                _lib.ptr(q), _lib.ptr(k), _lib.ptr(v), _lib.ptr(out), _lib.ptr(go), _lib.ptr(lse), ctypes.byref(dims),
+                _lib.ptr(bias), _lib.dtype_code(bias.dtype) if bias is not None else 0, _lib.ptr(code), ctx.pitch,
+                _lib.ptr(lut), _lib.ptr(key_pad), _lib.ptr(dq), _lib.ptr(dk), _lib.ptr(dv), ctypes.byref(gdims),
+                _lib.ptr(dq_accum), _lib.ptr(delta), _lib.ptr(g_bias), _lib.ptr(g_lut), _lib.stream()),
+                "mdt_biased_attn_bwd")
+        return dq, dk, dv, g_bias, None, g_lut, None
+
+
+def biased_attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, bias: Optional[torch.Tensor] = None,
+                     code: Optional[torch.Tensor] = None, lut: Optional[torch.Tensor] = None,
+                     key_padding_mask: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``softmax_fp32(q k^T + bias [+ key padding -> -inf]) v`` on the tcgen05 kernel.
+
+    ``q, k, v``: bf16 ``[B, T, H, 64]`` (any strides that are multiples of 8; ``q`` already scaled by
+    ``d^-0.5`` as at multihead_attention.py:137).  ``bias``: materialised ``[B,H,T,T]`` (f32 | bf16) **or**
+    ``code`` uint8 ``[B,T,pitch]`` with ``lut`` f32 ``[H,256]`` (bias = ``lut[h, code]``, code 255 = -inf).
+    Returns ``[B, T, H, 64]`` bf16 laid out like ``q``.
+    """
+    if bias is not None and code is not None:
+        raise ValueError("pass either a materialised bias or code+lut")
+    if code is not None and lut is None:
+        raise ValueError("code needs lut")
+    return _BiasedAttention.apply(q, k, v, bias, code, lut, key_padding_mask)
