@@ -1,0 +1,123 @@
+#!/usr/bin/env python
+"""BASELINE.json configs[3]: biased graph-attention kernel microbench -- 12 heads, d=64 (C=768), 64..1024
+comments + graph token, B=32, forward and forward+backward, plus the fusion-layer shapes (bottleneck
+tokens + text / patches).  CUDA-event timing on the launching stream, L2 flushed between iterations.
+
+    python benchmarks/attn_microbench.py [--T 65 129 ...] [--iters 50] [--mode code|bf16|none] [--json out.json]
+
+FLOP convention: fwd 4*B*H*T^2*d, bwd 8*B*H*T^2*d with the true T (the S recompute of the
+backward is not counted); fractions are against the measured bf16 peaks in MEASURED_PEAKS.json.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+
+import torch
+
+ROOT = os.path.abspath(os.path.join(os.path.dirname(__file__), ".."))
+sys.path.insert(0, ROOT)
+from multimodaldiscussiontransformer_b200 import ops  # noqa: E402
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.isfile(p):
+        d = json.load(open(p))
+        return d["bf16_tflops"], d.get("bf16_tflops_sustained", d["bf16_tflops"]), "measured"
+    return 1590.0, 1400.0, "fallback"
+
+
+def make_inputs(B, H, T, mode, seed=0):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    qkv = torch.randn(T, B, 3, H, 64, generator=g, device="cuda", dtype=torch.float32).bfloat16()
+    q, k, v = (qkv[:, :, i].permute(1, 0, 2, 3) for i in range(3))
+    q = (q.float() * 0.125).bfloat16()
+    kw = {}
+    n_valid = max(1, int(T * 0.75))  # 25 % trailing key padding
+    kw["key_padding_mask"] = (torch.arange(T, device="cuda")[None, :] >= n_valid).expand(B, T).contiguous()
+    if mode == "code":
+        pitch = (T + 15) // 16 * 16
+        code = torch.randint(1, 22, (B, T, pitch), generator=g, device="cuda", dtype=torch.int32)
+        far = torch.rand(B, T, pitch, generator=g, device="cuda") < 0.5   # hop distance >= spatial_pos_max
+        idx = torch.arange(T, device="cuda")
+        far[:, idx, idx] = False
+        code[far] = 255
+        code[:, 0, :] = 254
+        code[:, :, 0] = 254
+        kw["code"] = code.to(torch.uint8)
+        kw["lut"] = (torch.randn(H, 256, generator=g, device="cuda") * 0.1).requires_grad_(True)
+    elif mode in ("bf16", "f32"):
+        bias = torch.randn(B, H, T, T, generator=g, device="cuda") * 0.1
+        far = torch.rand(B, 1, T, T, generator=g, device="cuda") < 0.5
+        idx = torch.arange(T, device="cuda")
+        far[:, :, idx, idx] = False
+        bias = bias.masked_fill(far, float("-inf"))
+        kw["bias"] = (bias.bfloat16() if mode == "bf16" else bias).requires_grad_(True)
+    return q.detach().requires_grad_(True), k.detach().requires_grad_(True), v.detach().requires_grad_(True), kw
+
+
+def time_it(fn, iters, flush):
+    for _ in range(5):
+        fn()
+    torch.cuda.synchronize()
+    total = 0.0
+    for _ in range(iters):
+        if flush is not None:
+            flush.zero_()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        fn()
+        e.record()
+        e.synchronize()
+        total += s.elapsed_time(e)
+    return total / iters  # ms
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--T", type=int, nargs="*", default=[65, 129, 257, 513, 1025])
+    ap.add_argument("--B", type=int, default=32)
+    ap.add_argument("--H", type=int, default=12)
+    ap.add_argument("--iters", type=int, default=30)
+    ap.add_argument("--mode", default="code", choices=["code", "bf16", "f32", "none"])
+    ap.add_argument("--fusion-shapes", action="store_true", help="also (B'=4096,T=104) text and (410,201) image shapes")
+    ap.add_argument("--no-flush", action="store_true")
+    ap.add_argument("--json", default=None)
+    a = ap.parse_args()
+    burst, sustained, src = peaks()
+    flush = None if a.no_flush else torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    shapes = [(a.B, a.H, T) for T in a.T]
+    if a.fusion_shapes:
+        shapes += [(4096, a.H, 104), (410, a.H, 201)]
+    rows = []
+    for B, H, T in shapes:
+        q, k, v, kw = make_inputs(B, H, T, a.mode)
+        o = ops.biased_attention(q, k, v, **kw)
+        go = torch.randn_like(o)
+        inputs = [q, k, v] + [t for t in (kw.get("lut"), kw.get("bias")) if t is not None]
+
+        def fwd():
+            with torch.no_grad():
+                ops.biased_attention(q, k, v, **kw)
+
+        def bwd():
+            torch.autograd.grad(o, inputs, go, retain_graph=True)
+
+        f_ms = time_it(fwd, a.iters, flush)
+        b_ms = time_it(bwd, a.iters, flush)
+        ff, fb = 4.0 * B * H * T * T * 64, 8.0 * B * H * T * T * 64
+        row = dict(B=B, H=H, T=T, mode=a.mode, fwd_us=f_ms * 1e3, bwd_us=b_ms * 1e3, fwd_tflops=ff / f_ms / 1e9,
+                   bwd_tflops=fb / b_ms / 1e9, fwd_frac_burst=ff / f_ms / 1e9 / burst, bwd_frac_burst=fb / b_ms / 1e9 / burst,
+                   fwd_bwd_tflops=(ff + fb) / (f_ms + b_ms) / 1e9, peak_burst=burst, peak_sustained=sustained, peak_source=src,
+                   l2_flushed=flush is not None)
+        rows.append(row)
+        print(json.dumps(row))
+    if a.json:
+        json.dump(rows, open(a.json, "w"), indent=1)
+
+
+if __name__ == "__main__":
+    main()

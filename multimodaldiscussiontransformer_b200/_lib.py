@@ -74,7 +74,20 @@ def load():
     return _lib
 
 
+# C-ABI calls made so far (name -> count) and the kernels each one launches: bench.py reports
+# the number of this library's kernel launches inside its timed region from these.
+CALLS: dict = {}
+KERNELS_PER_CALL = {"mdt_apsp_batched": 1, "mdt_gen_edge_input": 1, "mdt_collate_graphs": 2, "mdt_attn_bias_fwd": 1,
+                    "mdt_attn_bias_bwd": 1, "mdt_biased_attn_fwd": 1, "mdt_biased_attn_bwd": 3, "mdt_node_feature_fwd": 1,
+                    "mdt_node_feature_bwd": 1, "mdt_gather_rows": 1, "mdt_scatter_rows": 1, "mdt_umma_selftest": 1}
+
+
+def kernel_launches() -> int:
+    return sum(KERNELS_PER_CALL.get(k, 1) * n for k, n in CALLS.items())
+
+
 def check(rc: int, what: str) -> None:
+    CALLS[what] = CALLS.get(what, 0) + 1
     if rc != 0:
         msg = load().mdt_last_error_string()
         raise RuntimeError(f"{what} failed ({rc}): {msg.decode() if msg else ''}")

@@ -15,6 +15,28 @@ import torch
 from . import _lib
 
 
+# When set to a list, the attention wrappers append (kind, start_event, end_event, B, H, T) around
+# their C-ABI call on the current stream: bench.py derives the kernels' live in-step durations from it.
+ATTN_EVENTS = None
+
+
+class _timed:
+    def __init__(self, kind, B, H, T):
+        self.rec = ATTN_EVENTS is not None
+        self.meta = (kind, B, H, T)
+
+    def __enter__(self):
+        if self.rec:
+            self.s = torch.cuda.Event(enable_timing=True)
+            self.e = torch.cuda.Event(enable_timing=True)
+            self.s.record()
+
+    def __exit__(self, *exc):
+        if self.rec:
+            self.e.record()
+            ATTN_EVENTS.append((self.meta[0], self.s, self.e) + self.meta[1:])
+
+
 def _require_cuda(*tensors) -> None:
     for t in tensors:
         if t is not None and not t.is_cuda:
@@ -230,7 +252,7 @@ class _BiasedAttention(torch.autograd.Function):
         out = _empty_like_layout(q)
         lse = torch.empty((B, H, T), dtype=torch.float32, device=q.device)
         dims = _attn_dims(q, k, v, out)
-        with torch.cuda.device(q.device):
+        with torch.cuda.device(q.device), _timed("fwd", B, H, T):
             _lib.check(lib.mdt_biased_attn_fwd(_lib.ptr(q), _lib.ptr(k), _lib.ptr(v), ctypes.byref(dims), _lib.ptr(bias),
                                                _lib.dtype_code(bias.dtype) if bias is not None else 0, _lib.ptr(code),
                                                pitch, _lib.ptr(lut) if code is not None else None, _lib.ptr(key_pad),
@@ -254,7 +276,7 @@ class _BiasedAttention(torch.autograd.Function):
         dims = _attn_dims(q, k, v, out)
         # grad_out is addressed through the "o" strides of gdims; dq/dk/dv through q/k/v strides of gdims
         gdims = _attn_dims(dq, dk, dv, go)
-        with torch.cuda.device(q.device):
+        with torch.cuda.device(q.device), _timed("bwd", B, H, T):
             _lib.check(lib.mdt_biased_attn_bwd(
                 _lib.ptr(q), _lib.ptr(k), _lib.ptr(v), _lib.ptr(out), _lib.ptr(go), _lib.ptr(lse), ctypes.byref(dims),
                 _lib.ptr(bias), _lib.dtype_code(bias.dtype) if bias is not None else 0, _lib.ptr(code), ctx.pitch,
