@@ -43,7 +43,18 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
 // generic-proxy writes to shared memory -> visible to the async proxy (TMA / tcgen05 operands)
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
+// register re-allocation between warpgroups (all 4 warps of a warpgroup execute it)
+template <int N> __device__ __forceinline__ void reg_dealloc() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
+template <int N> __device__ __forceinline__ void reg_alloc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
+
 // ---------------------------------------------------------------- TMA
+__device__ __forceinline__ void tma_load_2d_raw(void *dst, const CUtensorMap *m, uint64_t *bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+            smem_u32(dst)),
+        "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+        : "memory");
+}
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap *m) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");
 }
@@ -154,5 +165,7 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
 // bf16 tensor, innermost dimension contiguous, 128-byte swizzle; dims/strides innermost first.
 int make_tensor_map_bf16(CUtensorMap *map, const void *base, int rank, const uint64_t *dims, const uint64_t *strides_bytes,
                          const uint32_t *box);
+int make_tensor_map_u8_2d(CUtensorMap *map, const void *base, uint64_t cols, uint64_t rows, uint64_t pitch_bytes,
+                          uint32_t box_rows);
 
 }  // namespace mdt

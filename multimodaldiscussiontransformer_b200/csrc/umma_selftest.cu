@@ -45,6 +45,21 @@ int make_tensor_map_bf16(CUtensorMap *map, const void *base, int rank, const uin
     return MDT_OK;
 }
 
+// uint8 2-D tensor (rows x pitch bytes), 128-byte swizzle, box {128 bytes, box_rows}
+int make_tensor_map_u8_2d(CUtensorMap *map, const void *base, uint64_t cols, uint64_t rows, uint64_t pitch_bytes,
+                          uint32_t box_rows) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) return fail(MDT_ECUDA, "cuTensorMapEncodeTiled is not available from the driver");
+    MDT_REQUIRE(((uintptr_t)base & 15) == 0 && pitch_bytes % 16 == 0, "TMA needs a 16-byte aligned base and pitch");
+    const cuuint64_t gdim[2] = {cols, rows}, gstr[1] = {pitch_bytes};
+    const cuuint32_t bx[2] = {128, box_rows}, es[2] = {1, 1};
+    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void *>(base), gdim, gstr, bx, es,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(MDT_ECUDA, "cuTensorMapEncodeTiled(u8) failed with CUresult %d", (int)r);
+    return MDT_OK;
+}
+
 using namespace sm100;
 
 // smem map (bytes, 1024-aligned): A 0..16K | B 16K..32K | P 32K..64K | V 64K..80K | At 80K..112K | Bk 112K..128K
