@@ -46,5 +46,18 @@ inline int check_dims(const mdt_attn_dims *d, const char *who) {
     return MDT_OK;
 }
 
+// warp-specialised forward (attn_fwd2.cu): bias from byte codes or none
+struct Fwd2Args {
+    int B, H, T;
+    int has_code;
+    const float *lut;
+    const uint8_t *key_pad;
+    __nv_bfloat16 *out;
+    int64_t o_sb, o_st, o_sh;
+    float *lse;
+};
+int launch_fwd2(const CUtensorMap &mq, const CUtensorMap &mk, const CUtensorMap &mv, const CUtensorMap &mc, const Fwd2Args &a,
+                cudaStream_t st);
+
 }  // namespace attn
 }  // namespace mdt

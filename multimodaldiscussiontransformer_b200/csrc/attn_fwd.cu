@@ -304,7 +304,18 @@ extern "C" int mdt_biased_attn_fwd(const void *q, const void *k, const void *v, 
     a.o_sb = d->o_stride_b, a.o_st = d->o_stride_t, a.o_sh = d->o_stride_h;
     a.lse = lse;
     cudaStream_t st = as_stream(stream);
-    switch (bias_mode(bias, bias_dtype, code)) {
+    const int mode = bias_mode(bias, bias_dtype, code);
+    if ((mode == kBiasNone || mode == kBiasCode) && d->T > kTile) {  // warp-specialised kernel (attn_fwd2.cu): two query tiles per CTA
+        CUtensorMap mc = mq;
+        if (code)
+            if (int rc = make_tensor_map_u8_2d(&mc, code, (uint64_t)code_pitch, (uint64_t)d->B * d->T, (uint64_t)code_pitch, kTile))
+                return rc;
+        Fwd2Args a2;
+        a2.B = d->B, a2.H = d->H, a2.T = d->T, a2.has_code = code != nullptr, a2.lut = lut, a2.key_pad = key_pad;
+        a2.out = a.out, a2.o_sb = a.o_sb, a2.o_st = a.o_st, a2.o_sh = a.o_sh, a2.lse = lse;
+        return launch_fwd2(mq, mk, mv, mc, a2, st);
+    }
+    switch (mode) {
         case kBiasNone: return launch_fwd<kBiasNone>(mq, mk, mv, a, st);
         case kBiasF32: return launch_fwd<kBiasF32>(mq, mk, mv, a, st);
         case kBiasBF16: return launch_fwd<kBiasBF16>(mq, mk, mv, a, st);
