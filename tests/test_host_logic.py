@@ -1,0 +1,127 @@
+"""CPU checks of the host-side mirror of the reference interface (no kernel launches)."""
+
+from __future__ import annotations
+
+import json
+import os
+import sys
+from argparse import Namespace
+
+import numpy as np
+import pytest
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+G = os.path.join(HERE, "golden")
+for p in (G, os.path.join(HERE, "..", "oracle")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+import cases  # noqa: E402
+import mdt_oracle as orc  # noqa: E402
+
+
+def small_encoder():
+    from transformers import BertConfig, ViTConfig
+
+    from multimodaldiscussiontransformer_b200.modules import MultiGraphormerGraphEncoder
+
+    kw = dict(cases.COMMON_MODEL)
+    kw.update(num_fusion_layers=1, num_fusion_stack=1, num_graph_stack=1)
+    return MultiGraphormerGraphEncoder(multi_hop_max_dist=5, bert_config=BertConfig(num_labels=2, num_hidden_layers=3),
+                                       vit_config=ViTConfig(num_hidden_layers=3), **kw)
+
+
+def test_state_dict_keys_and_shapes_match_reference():
+    keys = json.load(open(os.path.join(G, "encoder_state_keys.json")))
+    mine = {k: list(v.shape) for k, v in small_encoder().state_dict().items()}
+    assert mine == keys
+
+
+def test_registry_names_match_reference():
+    import multimodaldiscussiontransformer_b200.criterions  # noqa: F401
+    import multimodaldiscussiontransformer_b200.models  # noqa: F401
+    from multimodaldiscussiontransformer_b200._registry import REGISTRY
+
+    assert "multi_graphormer" in REGISTRY["model"]
+    assert {"multi_graphormer", "multi_graphormer_base"} <= set(REGISTRY["arch"])
+    assert "node_cross_entropy" in REGISTRY["criterion"]
+
+
+def test_arch_defaults():
+    from multimodaldiscussiontransformer_b200.models import base_architecture, graphormer_base_architecture
+
+    a = Namespace()
+    graphormer_base_architecture(a)
+    assert (a.encoder_embed_dim, a.encoder_ffn_embed_dim, a.encoder_layers, a.encoder_attention_heads) == (80, 80, 12, 8)
+    assert a.num_bottleneck_tokens == 4 and a.num_fusion_layers == 4 and a.activation_fn == "gelu"
+    b = Namespace()
+    base_architecture(b)
+    assert (b.encoder_embed_dim, b.encoder_ffn_embed_dim, b.dropout, b.act_dropout) == (1024, 4096, 0.1, 0.0)
+
+
+def test_fused_bias_lut_equals_reference_bias():
+    """code + lut (what the attention kernel consumes) reproduces GraphAttnBias.forward exactly."""
+    from multimodaldiscussiontransformer_b200.modules import GraphAttnBias
+
+    items, spmax = cases.collate_items("ragged_sp5")
+    ref = orc.batch_to_torch(orc.collator(items, spmax))
+    gab = GraphAttnBias(12, 512 * 9, 512 * 3, 512, 128, 768, "multi_hop", 5, 2)
+    want = orc.graph_attn_bias(ref["attn_bias"], ref["spatial_pos"], gab.spatial_pos_encoder.weight,
+                               gab.graph_token_virtual_distance.weight)
+    # byte codes as the collate kernel defines them (include/mdt_b200.h): spatial_pos value, 254 virtual, 255 masked
+    B, T, _ = ref["attn_bias"].shape
+    code = torch.full((B, T, T), 254, dtype=torch.int64)
+    code[:, 1:, 1:] = ref["spatial_pos"].long()
+    code[torch.isneginf(ref["attn_bias"])] = 255
+    fused = gab.forward_fused({"bias_code": code.to(torch.uint8)})
+    got = fused.materialise()
+    assert torch.equal(torch.isneginf(got), torch.isneginf(want))
+    fin = ~torch.isneginf(want)
+    assert torch.allclose(got[fin], want[fin].float(), atol=1e-7)
+    got[fin].sum().backward()
+    assert float(gab.spatial_pos_encoder.weight.grad[0].abs().sum()) == 0.0  # padding_idx row: no gradient
+
+
+def test_host_batch_packing_matches_reference_collator():
+    from multimodaldiscussiontransformer_b200.data.collator import HostBatch
+
+    items, spmax = cases.collate_items("ragged_sp5")
+    ref = orc.collator(items, spmax)
+    hb = HostBatch(items, pin=False)
+    assert (hb.B, hb.N) == ref["x"].shape[:2]
+    mask = np.asarray(ref["x_token_mask"])
+    assert hb.n_real == int(mask.sum())
+    text = hb.tensors["text"].numpy()
+    np.testing.assert_array_equal(text[0], np.asarray(ref["x"])[mask])
+    np.testing.assert_array_equal(text[2], np.asarray(ref["x_attention_mask"])[mask])
+    np.testing.assert_array_equal(hb.tensors["flags"][0].numpy(), np.asarray(ref["x_image_indexes"]))
+    np.testing.assert_array_equal(hb.tensors["y"].numpy(), np.asarray(ref["y"]))
+    assert hb.nbytes() > 0
+
+
+def test_no_cpu_fallback():
+    from multimodaldiscussiontransformer_b200 import ops
+    from multimodaldiscussiontransformer_b200.data import algos
+
+    q = torch.zeros(1, 4, 2, 64, dtype=torch.bfloat16)
+    with pytest.raises(RuntimeError):
+        ops.biased_attention(q, q, q)
+    with pytest.raises(RuntimeError):
+        algos.floyd_warshall_batched(torch.zeros(1, 4, 4, dtype=torch.uint8))
+
+
+def test_criterion_matches_oracle_loss():
+    from multimodaldiscussiontransformer_b200.criterions import GraphPredictionNodeCrossEntropy
+
+    g = torch.Generator().manual_seed(0)
+    logits = torch.randn(9, 2, generator=g)
+    y = torch.tensor([1.0, 0.0, 1.0])
+    ym = torch.zeros(9, dtype=torch.bool)
+    ym[[1, 4, 7]] = True
+    crit = GraphPredictionNodeCrossEntropy(None, 1.5, 1.0)
+    model = lambda batched_data: (logits, None)
+    loss, n, log = crit(model, {"net_input": {"batched_data": {"x": torch.zeros(1, 9, 1), "y": y, "y_mask": ym}}})
+    want, n2 = orc.node_cross_entropy(logits, y, ym, 1.5, 1.0)
+    assert n == n2 == 3 and abs(float(loss) - float(want)) < 1e-6
+    agg = crit.aggregate([log])
+    assert 0.0 <= agg["accuracy"] <= 1.0 and "f1" in agg
