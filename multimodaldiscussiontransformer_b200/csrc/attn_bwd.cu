@@ -1,7 +1,8 @@
 // A6 backward of O = softmax(Q K^T + bias) V                       multihead_attention.py:168-199
 //
 //   delta[q] = sum_c dO[q,c] O[q,c]                                  (attn_delta_kernel)
-//   one CTA per (batch b, head h, 128-key tile); thread r owns key row r (= TMEM lane r); loop over
+//   one CTA per (batch b, head h, 128-key tile); 256 threads: threads r and r+128 own key row r (= TMEM
+//   lane r) and split the query columns of every tile between them; loop over
 //   128-query tiles i (Q_i, dO_i double-buffered by TMA):
 //     S^T  = K Q_i^T          tcgen05.mma 128x128x64                       -> TMEM cols [0,128)
 //     dP^T = V dO_i^T         tcgen05.mma 128x128x64                       -> TMEM cols [128,256)
@@ -20,7 +21,8 @@ namespace mdt {
 namespace attn {
 using namespace sm100;
 
-constexpr int kBins = 64;  // bias codes 0..62 have their own bin, MDT_CODE_VIRTUAL uses bin 63
+constexpr int kBins = 32;       // bias codes 0..30 have their own bin, MDT_CODE_VIRTUAL uses bin 31
+constexpr int kBwdThreads = 256;  // two warpgroups: each owns 64 of the 128 query columns of a tile
 
 struct BwdArgs {
     int B, H, T;
@@ -90,17 +92,17 @@ __global__ void attn_dq_convert_kernel(const float *__restrict__ acc, int B, int
 
 // ---------------------------------------------------------------- main backward kernel
 constexpr int kBwdSmemBase = 16384 * 2 /*K,V*/ + 2 * 16384 /*Q x2*/ + 2 * 16384 /*dO x2*/ + 32768 /*P^T*/ + 32768 /*dS^T*/;
-constexpr int kBwdBinsBytes = kBins * 128 * 4;
+constexpr int kBwdBinsBytes = kBins * kBwdThreads * 4;
 
 template <int MODE>
-__global__ void __launch_bounds__(128, 1)
+__global__ void __launch_bounds__(kBwdThreads, 1)
     attn_bwd_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__ CUtensorMap mk,
                     const __grid_constant__ CUtensorMap mv, const __grid_constant__ CUtensorMap mdo, const BwdArgs a) {
     extern __shared__ uint8_t smem_dyn[];
     uint8_t *smem = reinterpret_cast<uint8_t *>(((uintptr_t)smem_dyn + 1023) & ~(uintptr_t)1023);
     uint8_t *sK = smem, *sV = smem + 16384, *sQ = smem + 32768, *sdO = smem + 65536, *sPt = smem + 98304,
             *sdSt = smem + 131072;
-    float *bins = reinterpret_cast<float *>(smem + kBwdSmemBase);  // [kBins][128], only with grad_lut
+    float *bins = reinterpret_cast<float *>(smem + kBwdSmemBase);  // [kBins][256], only with grad_lut
     __shared__ __align__(8) uint64_t bar_kv, bar_qdo[2], bar_sp, bar_dq;
     __shared__ uint32_t tmem_base_s;
     __shared__ __align__(16) float s_nlse[2][128];   // -lse * log2(e); -inf for queries >= T
@@ -108,25 +110,27 @@ __global__ void __launch_bounds__(128, 1)
     __shared__ float s_lut[256];
 
     const int tid = threadIdx.x, warp = tid >> 5;
+    const int r = tid & 127, half = tid >> 7;  // key row inside the tile, which half of the query columns
     const int h = blockIdx.y, b = blockIdx.z;
     const int T = a.T;
     const int k0 = blockIdx.x * kTile;
-    const int key = k0 + tid;
+    const int key = k0 + r;
     const bool key_ok = key < T && !(a.key_pad != nullptr && a.key_pad[(size_t)b * T + key] != 0);
     const int nq = (T + kTile - 1) / kTile;
     const bool want_gbias = (MODE == kBiasF32 || MODE == kBiasBF16) && a.grad_bias != nullptr;
     const bool want_glut = MODE == kBiasCode && a.grad_lut != nullptr;
 
     auto stage_stats = [&](int i) {  // lse / delta of query tile i -> shared memory
-        const int qq = i * kTile + tid;
+        if (half != 0) return;
+        const int qq = i * kTile + r;
         float nl = neg_inf(), dl = 0.f;
         if (qq < T) {
-            const size_t r = ((size_t)b * a.H + h) * T + qq;
-            nl = -a.lse[r] * kLog2e;
-            dl = a.delta[r];
+            const size_t row = ((size_t)b * a.H + h) * T + qq;
+            nl = -a.lse[row] * kLog2e;
+            dl = a.delta[row];
         }
-        s_nlse[i & 1][tid] = nl;
-        s_delta[i & 1][tid] = dl;
+        s_nlse[i & 1][r] = nl;
+        s_delta[i & 1][r] = dl;
     };
 
     if (tid == 0) {
@@ -146,17 +150,16 @@ __global__ void __launch_bounds__(128, 1)
         tmem_relinquish();
     }
     if (MODE == kBiasCode) {
-        s_lut[tid] = a.lut[(size_t)h * 256 + tid];
-        s_lut[tid + 128] = (tid + 128 == MDT_CODE_MASKED) ? neg_inf() : a.lut[(size_t)h * 256 + tid + 128];
+        s_lut[tid] = (tid == MDT_CODE_MASKED) ? neg_inf() : a.lut[(size_t)h * 256 + tid];
         if (want_glut)
-            for (int c = 0; c < kBins; ++c) bins[c * 128 + tid] = 0.f;
+            for (int c = 0; c < kBins; ++c) bins[c * kBwdThreads + tid] = 0.f;
     }
     stage_stats(0);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = tmem_base_s;
-    const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
+    const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
     constexpr uint32_t cS = 0, cDP = 128, cDV = 256, cDK = 320, cDQ = 384;
     const uint32_t idesc_s = idesc_bf16(128, 128, 0, 0);
     const uint32_t idesc_kv = idesc_bf16(128, 64, 0, 1);
@@ -203,7 +206,7 @@ __global__ void __launch_bounds__(128, 1)
         const float *nl = s_nlse[i & 1];
         const float *dl = s_delta[i & 1];
 #pragma unroll 1
-        for (int cc = 0; cc < 4; ++cc) {
+        for (int cc = half * 2; cc < half * 2 + 2; ++cc) {
             float st[32], dp[32];
             tmem_ld_32x32(lane_base + cS + cc * 32, reinterpret_cast<uint32_t *>(st));
             tmem_ld_32x32(lane_base + cDP + cc * 32, reinterpret_cast<uint32_t *>(dp));
@@ -259,7 +262,7 @@ __global__ void __launch_bounds__(128, 1)
                 for (int i2 = 0; i2 < 32; ++i2) {
                     const uint32_t c = code_w[i2];
                     const uint32_t bin = c == MDT_CODE_VIRTUAL ? (uint32_t)(kBins - 1) : min(c, (uint32_t)(kBins - 2));
-                    bins[bin * 128 + tid] += dp[i2];  // masked codes carry dS = 0
+                    bins[bin * kBwdThreads + tid] += dp[i2];  // masked codes carry dS = 0
                 }
             }
             // ---- bf16 tiles [key][query], 128-byte swizzle, two 64-query halves
@@ -274,7 +277,7 @@ __global__ void __launch_bounds__(128, 1)
                 vd.y = pack_bf16x2(dp[u * 8 + 2], dp[u * 8 + 3]);
                 vd.z = pack_bf16x2(dp[u * 8 + 4], dp[u * 8 + 5]);
                 vd.w = pack_bf16x2(dp[u * 8 + 6], dp[u * 8 + 7]);
-                const uint32_t off = (cc >> 1) * 16384 + sw128_offset(tid, (cc & 1) * 4 + u);
+                const uint32_t off = (cc >> 1) * 16384 + sw128_offset(r, (cc & 1) * 4 + u);
                 *reinterpret_cast<uint4 *>(sPt + off) = vp;
                 *reinterpret_cast<uint4 *>(sdSt + off) = vd;
             }
@@ -312,50 +315,38 @@ __global__ void __launch_bounds__(128, 1)
         tc_fence_after();
         __syncwarp();
         {
-            float dq[64];
-            tmem_ld_32x32(lane_base + cDQ, reinterpret_cast<uint32_t *>(dq));
-            tmem_ld_32x32(lane_base + cDQ + 32, reinterpret_cast<uint32_t *>(dq) + 32);
+            float dq[32];  // this half's 32 of the 64 dQ columns of query row r
+            tmem_ld_32x32(lane_base + cDQ + half * 32, reinterpret_cast<uint32_t *>(dq));
             tmem_wait_ld();
-            if (tid < qvalid) {
-                float4 *dst = reinterpret_cast<float4 *>(a.dq_accum + (((size_t)b * a.H + h) * T + (q0 + tid)) * 64);
+            if (r < qvalid) {
+                float4 *dst = reinterpret_cast<float4 *>(a.dq_accum + (((size_t)b * a.H + h) * T + (q0 + r)) * 64 + half * 32);
 #pragma unroll
-                for (int u = 0; u < 16; ++u) atomicAdd(dst + u, make_float4(dq[u * 4], dq[u * 4 + 1], dq[u * 4 + 2], dq[u * 4 + 3]));
+                for (int u = 0; u < 8; ++u) atomicAdd(dst + u, make_float4(dq[u * 4], dq[u * 4 + 1], dq[u * 4 + 2], dq[u * 4 + 3]));
             }
         }
         tc_fence_before();  // the dQ columns are rewritten by the next tile's MMAs after the next __syncthreads
     }
 
-    // ---- epilogue: dK, dV rows of this key tile (bar_dq of the last tile covers every MMA)
+    // ---- epilogue: dK, dV rows of this key tile (bar_dq of the last tile covers every MMA); each half stores 32 columns
     {
-        float acc[64];
-        tmem_ld_32x32(lane_base + cDV, reinterpret_cast<uint32_t *>(acc));
-        tmem_ld_32x32(lane_base + cDV + 32, reinterpret_cast<uint32_t *>(acc) + 32);
-        tmem_wait_ld();
-        if (key < T) {
-            __nv_bfloat16 *p = a.dv + (size_t)b * a.dv_sb + (size_t)key * a.dv_st + (size_t)h * a.dv_sh;
+        float acc[32];
 #pragma unroll
-            for (int ch = 0; ch < 8; ++ch) {
-                uint4 v;
-                v.x = pack_bf16x2(acc[ch * 8 + 0], acc[ch * 8 + 1]);
-                v.y = pack_bf16x2(acc[ch * 8 + 2], acc[ch * 8 + 3]);
-                v.z = pack_bf16x2(acc[ch * 8 + 4], acc[ch * 8 + 5]);
-                v.w = pack_bf16x2(acc[ch * 8 + 6], acc[ch * 8 + 7]);
-                reinterpret_cast<uint4 *>(p)[ch] = v;
-            }
-        }
-        tmem_ld_32x32(lane_base + cDK, reinterpret_cast<uint32_t *>(acc));
-        tmem_ld_32x32(lane_base + cDK + 32, reinterpret_cast<uint32_t *>(acc) + 32);
-        tmem_wait_ld();
-        if (key < T) {
-            __nv_bfloat16 *p = a.dk + (size_t)b * a.dk_sb + (size_t)key * a.dk_st + (size_t)h * a.dk_sh;
+        for (int which = 0; which < 2; ++which) {
+            tmem_ld_32x32(lane_base + (which == 0 ? cDV : cDK) + half * 32, reinterpret_cast<uint32_t *>(acc));
+            tmem_wait_ld();
+            if (key < T) {
+                __nv_bfloat16 *p = which == 0 ? a.dv + (size_t)b * a.dv_sb + (size_t)key * a.dv_st + (size_t)h * a.dv_sh
+                                              : a.dk + (size_t)b * a.dk_sb + (size_t)key * a.dk_st + (size_t)h * a.dk_sh;
+                p += half * 32;
 #pragma unroll
-            for (int ch = 0; ch < 8; ++ch) {
-                uint4 v;
-                v.x = pack_bf16x2(acc[ch * 8 + 0], acc[ch * 8 + 1]);
-                v.y = pack_bf16x2(acc[ch * 8 + 2], acc[ch * 8 + 3]);
-                v.z = pack_bf16x2(acc[ch * 8 + 4], acc[ch * 8 + 5]);
-                v.w = pack_bf16x2(acc[ch * 8 + 6], acc[ch * 8 + 7]);
-                reinterpret_cast<uint4 *>(p)[ch] = v;
+                for (int ch = 0; ch < 4; ++ch) {
+                    uint4 v;
+                    v.x = pack_bf16x2(acc[ch * 8 + 0], acc[ch * 8 + 1]);
+                    v.y = pack_bf16x2(acc[ch * 8 + 2], acc[ch * 8 + 3]);
+                    v.z = pack_bf16x2(acc[ch * 8 + 4], acc[ch * 8 + 5]);
+                    v.w = pack_bf16x2(acc[ch * 8 + 6], acc[ch * 8 + 7]);
+                    reinterpret_cast<uint4 *>(p)[ch] = v;
+                }
             }
         }
     }
@@ -363,9 +354,9 @@ __global__ void __launch_bounds__(128, 1)
     __syncthreads();
     if (warp == 0) tmem_dealloc(tmem, 512);
     if (MODE == kBiasCode && want_glut && tid < kBins) {
-        // bin `tid`: sum over the 128 per-thread copies (rotated start keeps the banks distinct)
+        // bin `tid`: sum over the 256 per-thread copies (rotated start keeps the banks distinct)
         float sum = 0.f;
-        for (int t = 0; t < 128; ++t) sum += bins[tid * 128 + ((t + tid) & 127)];
+        for (int t = 0; t < kBwdThreads; ++t) sum += bins[tid * kBwdThreads + ((t + tid) & (kBwdThreads - 1))];
         const int code = tid == kBins - 1 ? MDT_CODE_VIRTUAL : tid;
         if (sum != 0.f) atomicAdd(a.grad_lut + (size_t)h * 256 + code, sum);
     }
@@ -381,7 +372,7 @@ static int launch_bwd(const CUtensorMap &mq, const CUtensorMap &mk, const CUtens
         configured = smem;
     }
     dim3 grid((a.T + kTile - 1) / kTile, a.H, a.B);
-    attn_bwd_kernel<MODE><<<grid, 128, smem, st>>>(mq, mk, mv, mdo, a);
+    attn_bwd_kernel<MODE><<<grid, kBwdThreads, smem, st>>>(mq, mk, mv, mdo, a);
     MDT_CHECK_CUDA(cudaGetLastError());
     return MDT_OK;
 }
