@@ -305,7 +305,7 @@ extern "C" int mdt_biased_attn_fwd(const void *q, const void *k, const void *v, 
     a.lse = lse;
     cudaStream_t st = as_stream(stream);
     const int mode = bias_mode(bias, bias_dtype, code);
-    if ((mode == kBiasNone || mode == kBiasCode) && d->T > kTile) {  // warp-specialised kernel (attn_fwd2.cu): two query tiles per CTA
+    if ((mode == kBiasNone || mode == kBiasCode) && d->T > kTile && d->T <= 8192) {  // warp-specialised kernel (attn_fwd2.cu): two query tiles per CTA
         CUtensorMap mc = mq;
         if (code)
             if (int rc = make_tensor_map_u8_2d(&mc, code, (uint64_t)code_pitch, (uint64_t)d->B * d->T, (uint64_t)code_pitch, kTile))

@@ -21,7 +21,8 @@ using namespace sm100;
 constexpr int kF2Threads = 384;
 constexpr int kF2Stage = 4 * 16384;                                 // K, V, code0, code1
 constexpr int kF2Smem = 2 * 16384 + 2 * kF2Stage + 2 * 32768 + 1024; // + alignment slack
-constexpr float kF2Rescale = 8.0f * kLn2;
+constexpr float kF2Rescale = 8.0f;   // log2 units: P may reach 2^8 before O is rescaled
+constexpr int kF2MaxT = 8192;         // key-mask bitmap of the whole row lives in shared memory
 
 struct F2Bars {
     uint64_t q_full, k_full[2], v_full[2], c_full[2], kv_empty[2], c_empty[2];
@@ -39,13 +40,17 @@ __global__ void __launch_bounds__(kF2Threads, 1)
     uint8_t *sP = sStage + 2 * kF2Stage;      // 2 x 32 KB
     __shared__ __align__(8) F2Bars bars;
     __shared__ uint32_t tmem_base_s;
-    __shared__ float s_lut[256];
+    // 64-entry table in log2 units, indexed by (code & 63): spatial codes 0..61, 62 = MDT_CODE_VIRTUAL & 63,
+    // 63 = MDT_CODE_MASKED & 63 (-inf).  Codes 62..253 are reserved (the collate kernel emits <= 21).
+    __shared__ float s_lut[64];
+    __shared__ uint32_t s_kmask[kF2MaxT / 32];  // bit set = key masked (padding or >= T)
+    __shared__ int s_last_word;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int h = blockIdx.y, b = blockIdx.z;
     const int T = a.T;
     const int q_base = blockIdx.x * 2 * kTile;
-    const int nkv = (T + kTile - 1) / kTile;
+    const int nkv_all = (T + kTile - 1) / kTile;
     const bool tile1_live = q_base + kTile < T;  // a CTA at the tail may own a single query tile
 
     if (tid == 0) {
@@ -71,11 +76,27 @@ __global__ void __launch_bounds__(kF2Threads, 1)
         tmem_alloc(&tmem_base_s, 512);
         tmem_relinquish();
     }
-    if (HAS_CODE && tid < 256) s_lut[tid] = (tid == MDT_CODE_MASKED) ? neg_inf() : a.lut[(size_t)h * 256 + tid];
+    if (HAS_CODE && tid < 64) {
+        const int src = tid == 62 ? MDT_CODE_VIRTUAL : tid;
+        s_lut[tid] = tid == 63 ? neg_inf() : a.lut[(size_t)h * 256 + src] * kLog2e;
+    }
+    if (tid == 0) s_last_word = -1;
+    __syncthreads();
+    for (int k0 = warp * 32; k0 < nkv_all * kTile; k0 += kF2Threads) {
+        const int kk = k0 + lane;
+        const bool masked = kk >= T || (a.key_pad != nullptr && a.key_pad[(size_t)b * T + kk] != 0);
+        const uint32_t bal = __ballot_sync(0xffffffffu, masked);
+        if (lane == 0) {
+            s_kmask[k0 >> 5] = bal;
+            if (bal != 0xffffffffu) atomicMax(&s_last_word, k0 >> 5);
+        }
+    }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = tmem_base_s;
+    // key tiles after the last unmasked key contribute exactly 0 to every row: never loaded or multiplied
+    const int nkv = s_last_word < 0 ? 1 : (s_last_word >> 2) + 1;
 
     if (warp >= 8) {
         // ------------------------------------------------------------------ producer / MMA warpgroup
@@ -150,19 +171,15 @@ __global__ void __launch_bounds__(kF2Threads, 1)
         const bool warp_live = __any_sync(0xffffffffu, row_ok);  // warps past the end only keep the barriers moving
         const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
         const uint32_t tS = lane_base + t * 128, tO = lane_base + 256 + t * 64;
-        uint8_t *myP = sP + t * 32768;
-        float m_used = neg_inf(), l = 0.f;
+        const uint32_t myP = smem_u32(sP + t * 32768);
+        float m_used = neg_inf(), l = 0.f;   // m_used in log2 units (scores are scaled by log2 e on the fly)
+        const uint32_t lut_base = smem_u32(s_lut);
 
         for (int j = 0; j < nkv; ++j) {
-            const int s = j & 1, k0 = j * kTile;
-            // key mask of this tile: lane i of every warp tests keys k0 + 32 c + i
+            const int s = j & 1;
             uint32_t kmask[4];
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                const int kk = k0 + c * 32 + lane;
-                const bool masked = kk >= T || (a.key_pad != nullptr && a.key_pad[(size_t)b * T + kk] != 0);
-                kmask[c] = __ballot_sync(0xffffffffu, masked);
-            }
+            for (int c = 0; c < 4; ++c) kmask[c] = s_kmask[j * 4 + c];
             float sc[128];
             mbar_wait(&bars.s_full[t], j & 1);
             tc_fence_after();
@@ -172,51 +189,63 @@ __global__ void __launch_bounds__(kF2Threads, 1)
             tmem_wait_ld();
             tc_fence_before();
             mbar_arrive(&bars.s_free[t]);              // S_t may be overwritten by the next Q_t K^T
-            if (HAS_CODE) {
-                mbar_wait(&bars.c_full[s], (j >> 1) & 1);
-                if (warp_live) {
-                    const uint8_t *crow = sStage + s * kF2Stage + 32768 + t * 16384;
+            if (HAS_CODE) mbar_wait(&bars.c_full[s], (j >> 1) & 1);
+            // ---- pass 1: x = s * log2(e) + lut[code] (log2 units), key mask, row maximum.
+            // Chunks of 32 keys that are masked for every row are skipped in both passes.
+            float mx0 = neg_inf(), mx1 = neg_inf();
+            if (warp_live) {
+                const uint32_t crow = smem_u32(sStage + s * kF2Stage + 32768 + t * 16384);
 #pragma unroll
-                    for (int u = 0; u < 8; ++u) {
-                        if (kmask[u >> 1] != 0xffffffffu) {
-                            const uint4 w = *reinterpret_cast<const uint4 *>(crow + sw128_offset(r, u));
-                            const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+                for (int c = 0; c < 4; ++c) {
+                    if (kmask[c] != 0xffffffffu) {
 #pragma unroll
-                            for (int i = 0; i < 16; ++i) sc[u * 16 + i] += s_lut[(ww[i >> 2] >> ((i & 3) * 8)) & 0xffu];
+                        for (int u = 2 * c; u < 2 * c + 2; ++u) {
+                            if (HAS_CODE) {
+                                const uint4 w = lds_u4(crow + sw128_offset(r, u));
+                                const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+                                for (int g = 0; g < 4; ++g) {
+                                    const uint32_t wm = (ww[g] << 2) & 0xfcfcfcfcu;   // byte -> 4 * (code & 63)
+                                    const float l0 = lds_f32(lut_base + __byte_perm(wm, 0, 0x4440));
+                                    const float l1 = lds_f32(lut_base + __byte_perm(wm, 0, 0x4441));
+                                    const float l2 = lds_f32(lut_base + __byte_perm(wm, 0, 0x4442));
+                                    const float l3 = lds_f32(lut_base + __byte_perm(wm, 0, 0x4443));
+                                    float *x = sc + u * 16 + g * 4;
+                                    ffma2(x[0], x[1], x[0], x[1], kLog2e, kLog2e, l0, l1);
+                                    ffma2(x[2], x[3], x[2], x[3], kLog2e, kLog2e, l2, l3);
+                                }
+                            } else {
+#pragma unroll
+                                for (int g = 0; g < 8; ++g) {
+                                    float *x = sc + u * 16 + g * 2;
+                                    ffma2(x[0], x[1], x[0], x[1], kLog2e, kLog2e, 0.f, 0.f);
+                                }
+                            }
+                        }
+                        if (kmask[c] != 0) {
+#pragma unroll
+                            for (int i = 0; i < 32; ++i)
+                                if (kmask[c] & (1u << i)) sc[c * 32 + i] = neg_inf();
+                        }
+#pragma unroll
+                        for (int i = 0; i < 32; i += 4) {
+                            mx0 = fmax3(mx0, sc[c * 32 + i], sc[c * 32 + i + 1]);
+                            mx1 = fmax3(mx1, sc[c * 32 + i + 2], sc[c * 32 + i + 3]);
                         }
                     }
                 }
-                mbar_arrive(&bars.c_empty[s]);
             }
+            if (HAS_CODE) mbar_arrive(&bars.c_empty[s]);
             float alpha = 1.f;
             bool grow = false;
             if (warp_live) {
-#pragma unroll
-                for (int c = 0; c < 4; ++c) {
-                    const uint32_t w = kmask[c];
-                    if (w != 0) {
-#pragma unroll
-                        for (int i = 0; i < 32; ++i)
-                            if (w & (1u << i)) sc[c * 32 + i] = neg_inf();
-                    }
-                }
-                float mx = neg_inf();
-#pragma unroll
-                for (int i = 0; i < 128; ++i) mx = fmaxf(mx, sc[i]);
+                const float mx = fmaxf(mx0, mx1);
                 grow = mx > m_used + kF2Rescale;       // also true for the first finite maximum
                 if (grow) {
-                    alpha = ex2((m_used - mx) * kLog2e);
+                    alpha = ex2(m_used - mx);
                     m_used = mx;
                     l *= alpha;
                 }
-                const float msc = (m_used == neg_inf()) ? 0.f : m_used * kLog2e;
-                float sum = 0.f;
-#pragma unroll
-                for (int i = 0; i < 128; ++i) {
-                    sc[i] = ex2(fmaf(sc[i], kLog2e, -msc));
-                    sum += sc[i];
-                }
-                l += sum;
             }
             // P_t (shared) and O_t (TMEM) are free once P V of the previous key tile has completed
             if (j > 0) {
@@ -236,16 +265,37 @@ __global__ void __launch_bounds__(kF2Threads, 1)
                     tmem_wait_st();
                 }
             }
+            // ---- pass 2: p = 2^(x - m), row sum, bf16 P tile (128-byte swizzle, K-major A operand of P V)
             if (warp_live) {
+                const float nm = (m_used == neg_inf()) ? 0.f : -m_used;
+                float sum0 = 0.f, sum1 = 0.f;
 #pragma unroll
-                for (int ch = 0; ch < 16; ++ch) {
-                    uint4 v;
-                    v.x = pack_bf16x2(sc[ch * 8 + 0], sc[ch * 8 + 1]);
-                    v.y = pack_bf16x2(sc[ch * 8 + 2], sc[ch * 8 + 3]);
-                    v.z = pack_bf16x2(sc[ch * 8 + 4], sc[ch * 8 + 5]);
-                    v.w = pack_bf16x2(sc[ch * 8 + 6], sc[ch * 8 + 7]);
-                    *reinterpret_cast<uint4 *>(myP + (ch >> 3) * 16384 + sw128_offset(r, ch & 7)) = v;
+                for (int c = 0; c < 4; ++c) {
+                    if (kmask[c] != 0xffffffffu) {
+#pragma unroll
+                        for (int ch = 4 * c; ch < 4 * c + 4; ++ch) {
+                            float *x = sc + ch * 8;
+#pragma unroll
+                            for (int i = 0; i < 8; i += 2) {
+                                fadd2(x[i], x[i + 1], x[i], x[i + 1], nm, nm);
+                                x[i] = ex2(x[i]);
+                                x[i + 1] = ex2(x[i + 1]);
+                                fadd2(sum0, sum1, sum0, sum1, x[i], x[i + 1]);
+                            }
+                            uint4 v;
+                            v.x = pack_bf16x2(x[0], x[1]);
+                            v.y = pack_bf16x2(x[2], x[3]);
+                            v.z = pack_bf16x2(x[4], x[5]);
+                            v.w = pack_bf16x2(x[6], x[7]);
+                            sts_u4(myP + (ch >> 3) * 16384 + sw128_offset(r, ch & 7), v);
+                        }
+                    } else {
+#pragma unroll
+                        for (int ch = 4 * c; ch < 4 * c + 4; ++ch)
+                            sts_u4(myP + (ch >> 3) * 16384 + sw128_offset(r, ch & 7), make_uint4(0, 0, 0, 0));
+                    }
                 }
+                l += sum0 + sum1;
             }
             fence_proxy_async();
             tc_fence_before();
@@ -272,7 +322,7 @@ __global__ void __launch_bounds__(kF2Threads, 1)
                     v.w = pack_bf16x2(o[ch * 8 + 6] * inv, o[ch * 8 + 7] * inv);
                     reinterpret_cast<uint4 *>(op)[ch] = v;
                 }
-                if (a.lse) a.lse[((size_t)b * a.H + h) * T + q] = l > 0.f ? m_used + logf(l) : __int_as_float(0x7f800000);
+                if (a.lse) a.lse[((size_t)b * a.H + h) * T + q] = l > 0.f ? m_used * kLn2 + logf(l) : __int_as_float(0x7f800000);
             }
         }
     }
