@@ -59,21 +59,23 @@ def make_inputs(B, H, T, mode, seed=0):
     return q.detach().requires_grad_(True), k.detach().requires_grad_(True), v.detach().requires_grad_(True), kw
 
 
-def time_it(fn, iters, flush):
+def time_it(fn, iters, flush, kind):
+    """Mean device time (ms) of the C-ABI call of `kind` inside fn(): CUDA events recorded by the wrapper right around
+    the library call (ops.ATTN_EVENTS) on the launching stream, the host kept ahead of the device by a GPU-side spin, so
+    the bracket holds the library's kernels only (no torch glue kernels, no launch gaps)."""
     for _ in range(5):
         fn()
     torch.cuda.synchronize()
-    total = 0.0
+    ops.ATTN_EVENTS = []
     for _ in range(iters):
         if flush is not None:
             flush.zero_()
-        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        s.record()
+        torch.cuda._sleep(400000)  # ~0.2 ms of GPU spin
         fn()
-        e.record()
-        e.synchronize()
-        total += s.elapsed_time(e)
-    return total / iters  # ms
+        torch.cuda.synchronize()
+    ev = [s.elapsed_time(e) for k, s, e, *_ in ops.ATTN_EVENTS if k == kind]
+    ops.ATTN_EVENTS = None
+    return sum(ev) / len(ev)  # ms
 
 
 def main():
@@ -106,8 +108,8 @@ def main():
         def bwd():
             torch.autograd.grad(o, inputs, go, retain_graph=True)
 
-        f_ms = time_it(fwd, a.iters, flush)
-        b_ms = time_it(bwd, a.iters, flush)
+        f_ms = time_it(fwd, a.iters, flush, "fwd")
+        b_ms = time_it(bwd, a.iters, flush, "bwd")
         ff, fb = 4.0 * B * H * T * T * 64, 8.0 * B * H * T * T * 64
         row = dict(B=B, H=H, T=T, mode=a.mode, fwd_us=f_ms * 1e3, bwd_us=b_ms * 1e3, fwd_tflops=ff / f_ms / 1e9,
                    bwd_tflops=fb / b_ms / 1e9, fwd_frac_burst=ff / f_ms / 1e9 / burst, bwd_frac_burst=fb / b_ms / 1e9 / burst,

@@ -139,6 +139,10 @@ int mdt_biased_attn_fwd(const void *q, const void *k, const void *v, const mdt_a
                         const void *bias, int bias_dtype, const uint8_t *code, int code_pitch,
                         const float *lut, const uint8_t *key_pad, void *out, float *lse, mdt_stream_t stream);
 
+/* Diagnostics (no reference counterpart): when dev_buffer is non-null the persistent forward writes 64
+ * %globaltimer stamps per CTA into it (u64 [n_ctas,64], device memory); null switches tracing off. */
+int mdt_debug_attn_trace(unsigned long long *dev_buffer);
+
 int mdt_biased_attn_bwd(const void *q, const void *k, const void *v, const void *out, const void *grad_out,
                         const float *lse, const mdt_attn_dims *dims, const void *bias, int bias_dtype,
                         const uint8_t *code, int code_pitch, const float *lut, const uint8_t *key_pad,

@@ -46,7 +46,7 @@ inline int check_dims(const mdt_attn_dims *d, const char *who) {
     return MDT_OK;
 }
 
-// warp-specialised forward (attn_fwd2.cu): bias from byte codes or none
+// persistent warp-specialised forward (attn_fwd3.cu): bias from byte codes or none
 struct Fwd2Args {
     int B, H, T;
     int has_code;
@@ -55,9 +55,12 @@ struct Fwd2Args {
     __nv_bfloat16 *out;
     int64_t o_sb, o_st, o_sh;
     float *lse;
+    unsigned long long *trace;  // diagnostics: per-CTA globaltimer stamps (mdt_debug_attn_trace), else null
 };
-int launch_fwd2(const CUtensorMap &mq, const CUtensorMap &mk, const CUtensorMap &mv, const CUtensorMap &mc, const Fwd2Args &a,
+constexpr int kFwd3MaxT = 4096;  // the key-mask bitmap of a whole row lives in shared memory (attn_fwd3.cu)
+int launch_fwd3(const CUtensorMap &mq, const CUtensorMap &mk, const CUtensorMap &mv, const CUtensorMap &mc, const Fwd2Args &a,
                 cudaStream_t st);
+
 
 }  // namespace attn
 }  // namespace mdt

@@ -278,6 +278,13 @@ static int launch_fwd(const CUtensorMap &mq, const CUtensorMap &mk, const CUtens
 using namespace mdt;
 using namespace mdt::attn;
 
+// diagnostics only: per-CTA globaltimer stamps of the persistent forward (64 x u64 per CTA, device memory), or null
+static unsigned long long *g_attn_trace = nullptr;
+extern "C" int mdt_debug_attn_trace(unsigned long long *dev_buffer) {
+    g_attn_trace = dev_buffer;
+    return MDT_OK;
+}
+
 extern "C" int mdt_biased_attn_fwd(const void *q, const void *k, const void *v, const mdt_attn_dims *d, const void *bias,
                                    int bias_dtype, const uint8_t *code, int code_pitch, const float *lut,
                                    const uint8_t *key_pad, void *out, float *lse, mdt_stream_t stream) {
@@ -305,7 +312,7 @@ extern "C" int mdt_biased_attn_fwd(const void *q, const void *k, const void *v, 
     a.lse = lse;
     cudaStream_t st = as_stream(stream);
     const int mode = bias_mode(bias, bias_dtype, code);
-    if ((mode == kBiasNone || mode == kBiasCode) && d->T > kTile && d->T <= 8192) {  // warp-specialised kernel (attn_fwd2.cu): two query tiles per CTA
+    if ((mode == kBiasNone || mode == kBiasCode) && d->T > kTile && d->T <= kFwd3MaxT) {  // persistent warp-specialised kernel (attn_fwd3.cu)
         CUtensorMap mc = mq;
         if (code)
             if (int rc = make_tensor_map_u8_2d(&mc, code, (uint64_t)code_pitch, (uint64_t)d->B * d->T, (uint64_t)code_pitch, kTile))
@@ -313,7 +320,8 @@ extern "C" int mdt_biased_attn_fwd(const void *q, const void *k, const void *v, 
         Fwd2Args a2;
         a2.B = d->B, a2.H = d->H, a2.T = d->T, a2.has_code = code != nullptr, a2.lut = lut, a2.key_pad = key_pad;
         a2.out = a.out, a2.o_sb = a.o_sb, a2.o_st = a.o_st, a2.o_sh = a.o_sh, a2.lse = lse;
-        return launch_fwd2(mq, mk, mv, mc, a2, st);
+        a2.trace = g_attn_trace;
+        return launch_fwd3(mq, mk, mv, mc, a2, st);
     }
     switch (mode) {
         case kBiasNone: return launch_fwd<kBiasNone>(mq, mk, mv, a, st);
