@@ -21,7 +21,7 @@ namespace mdt {
 namespace attn {
 using namespace sm100;
 
-constexpr int kBins = 32;       // bias codes 0..30 have their own bin, MDT_CODE_VIRTUAL uses bin 31
+constexpr int kBins = 24;       // bias codes 0..22 have their own bin (the collate kernel emits <= 21), MDT_CODE_VIRTUAL uses bin 23
 constexpr int kBwdThreads = 256;  // two warpgroups: each owns 64 of the 128 query columns of a tile
 
 struct BwdArgs {
@@ -92,17 +92,20 @@ __global__ void attn_dq_convert_kernel(const float *__restrict__ acc, int B, int
 
 // ---------------------------------------------------------------- main backward kernel
 constexpr int kBwdSmemBase = 16384 * 2 /*K,V*/ + 2 * 16384 /*Q x2*/ + 2 * 16384 /*dO x2*/ + 32768 /*P^T*/ + 32768 /*dS^T*/;
+constexpr int kBwdCodeBytes = 2 * 16384;  // byte-code tiles [query][key] of two query tiles (TMA, 128-byte swizzle)
 constexpr int kBwdBinsBytes = kBins * kBwdThreads * 4;
 
 template <int MODE>
 __global__ void __launch_bounds__(kBwdThreads, 1)
     attn_bwd_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__ CUtensorMap mk,
-                    const __grid_constant__ CUtensorMap mv, const __grid_constant__ CUtensorMap mdo, const BwdArgs a) {
+                    const __grid_constant__ CUtensorMap mv, const __grid_constant__ CUtensorMap mdo,
+                    const __grid_constant__ CUtensorMap mc, const BwdArgs a) {
     extern __shared__ uint8_t smem_dyn[];
     uint8_t *smem = reinterpret_cast<uint8_t *>(((uintptr_t)smem_dyn + 1023) & ~(uintptr_t)1023);
     uint8_t *sK = smem, *sV = smem + 16384, *sQ = smem + 32768, *sdO = smem + 65536, *sPt = smem + 98304,
             *sdSt = smem + 131072;
-    float *bins = reinterpret_cast<float *>(smem + kBwdSmemBase);  // [kBins][256], only with grad_lut
+    uint8_t *sCode = smem + kBwdSmemBase;                                           // 2 x 16 KB, only with codes
+    float *bins = reinterpret_cast<float *>(smem + kBwdSmemBase + kBwdCodeBytes);  // [kBins][256], only with grad_lut
     __shared__ __align__(8) uint64_t bar_kv, bar_qdo[2], bar_sp, bar_dq;
     __shared__ uint32_t tmem_base_s;
     __shared__ __align__(16) float s_nlse[2][128];   // -lse * log2(e); -inf for queries >= T
@@ -119,6 +122,19 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
     const int nq = (T + kTile - 1) / kTile;
     const bool want_gbias = (MODE == kBiasF32 || MODE == kBiasBF16) && a.grad_bias != nullptr;
     const bool want_glut = MODE == kBiasCode && a.grad_lut != nullptr;
+    const bool warp_keys = __any_sync(0xffffffffu, key_ok);  // a warp whose 32 keys are all masked only writes zeros
+
+    // A key tile without a single live key has dK = dV = 0 and adds nothing to dQ or the LUT gradient.
+    // (The materialised-bias modes still have to write their d-bias zeros, so they take the long way.)
+    if ((MODE == kBiasCode || MODE == kBiasNone) && !__syncthreads_or(key_ok ? 1 : 0)) {
+        if (key < T) {
+            uint4 *pk = reinterpret_cast<uint4 *>(a.dk + (size_t)b * a.dk_sb + (size_t)key * a.dk_st + (size_t)h * a.dk_sh + half * 32);
+            uint4 *pv = reinterpret_cast<uint4 *>(a.dv + (size_t)b * a.dv_sb + (size_t)key * a.dv_st + (size_t)h * a.dv_sh + half * 32);
+#pragma unroll
+            for (int ch = 0; ch < 4; ++ch) pk[ch] = pv[ch] = make_uint4(0, 0, 0, 0);
+        }
+        return;
+    }
 
     auto stage_stats = [&](int i) {  // lse / delta of query tile i -> shared memory
         if (half != 0) return;
@@ -144,6 +160,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
         tma_prefetch_desc(&mk);
         tma_prefetch_desc(&mv);
         tma_prefetch_desc(&mdo);
+        if (MODE == kBiasCode) tma_prefetch_desc(&mc);
     }
     if (warp == 0) {
         tmem_alloc(&tmem_base_s, 512);
@@ -177,9 +194,10 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
         umma_commit(&bar_sp);
     };
     auto load_qdo = [&](int i) {  // tid 0
-        mbar_expect_tx(&bar_qdo[i & 1], 32768);
+        mbar_expect_tx(&bar_qdo[i & 1], MODE == kBiasCode ? 49152 : 32768);
         tma_load_4d(sQ + (i & 1) * 16384, &mq, &bar_qdo[i & 1], 0, i * kTile, h, b);
         tma_load_4d(sdO + (i & 1) * 16384, &mdo, &bar_qdo[i & 1], 0, i * kTile, h, b);
+        if (MODE == kBiasCode) tma_load_2d_raw(sCode + (i & 1) * 16384, &mc, &bar_qdo[i & 1], k0, b * T + i * kTile);
     };
 
     if (tid == 0) {
@@ -202,11 +220,21 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
         mbar_wait(&bar_sp, i & 1);
         tc_fence_after();
         __syncwarp();
+        if (MODE == kBiasCode) mbar_wait(&bar_qdo[i & 1], (i >> 1) & 1);  // the code tile was written by TMA
 
         const float *nl = s_nlse[i & 1];
         const float *dl = s_delta[i & 1];
 #pragma unroll 1
         for (int cc = half * 2; cc < half * 2 + 2; ++cc) {
+            if (!warp_keys && !want_gbias) {  // 32 masked keys: P^T = dS^T = 0 for these rows
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const uint32_t off = (cc >> 1) * 16384 + sw128_offset(r, (cc & 1) * 4 + u);
+                    *reinterpret_cast<uint4 *>(sPt + off) = make_uint4(0, 0, 0, 0);
+                    *reinterpret_cast<uint4 *>(sdSt + off) = make_uint4(0, 0, 0, 0);
+                }
+                continue;
+            }
             float st[32], dp[32];
             tmem_ld_32x32(lane_base + cS + cc * 32, reinterpret_cast<uint32_t *>(st));
             tmem_ld_32x32(lane_base + cDP + cc * 32, reinterpret_cast<uint32_t *>(dp));
@@ -224,11 +252,14 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
                     }
                 }
             } else if (MODE == kBiasCode) {
-                const uint8_t *cp = a.code + ((size_t)b * T + (q0 + cc * 32)) * (size_t)a.code_pitch + key;
+                // byte (query cc*32+i2, key r) of the [query][key] tile: 128-byte rows, 16-byte chunks XOR-swizzled by row & 7
+                const uint32_t cbase = smem_u32(sCode + (i & 1) * 16384) + cc * 4096 + (r & 15);
+                const uint32_t rchunk = (uint32_t)(r >> 4) << 4;
 #pragma unroll
                 for (int i2 = 0; i2 < 32; ++i2) {
-                    uint32_t c = MDT_CODE_MASKED;
-                    if (key < T && cc * 32 + i2 < qvalid) c = __ldg(cp + (size_t)i2 * a.code_pitch);
+                    uint32_t c;
+                    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(c) : "r"(cbase + i2 * 128 + (rchunk ^ ((i2 & 7) << 4))) : "memory");
+                    if (!(key < T && cc * 32 + i2 < qvalid)) c = MDT_CODE_MASKED;
                     code_w[i2] = c;
                     st[i2] += s_lut[c];
                 }
@@ -364,15 +395,15 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
 
 template <int MODE>
 static int launch_bwd(const CUtensorMap &mq, const CUtensorMap &mk, const CUtensorMap &mv, const CUtensorMap &mdo,
-                      const BwdArgs &a, cudaStream_t st) {
-    const int smem = kBwdSmemBase + 1024 + ((MODE == kBiasCode && a.grad_lut) ? kBwdBinsBytes : 0);
+                      const CUtensorMap &mc, const BwdArgs &a, cudaStream_t st) {
+    const int smem = kBwdSmemBase + 1024 + (MODE == kBiasCode ? kBwdCodeBytes : 0) + ((MODE == kBiasCode && a.grad_lut) ? kBwdBinsBytes : 0);
     static int configured = 0;
     if (configured < smem) {
         MDT_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         configured = smem;
     }
     dim3 grid((a.T + kTile - 1) / kTile, a.H, a.B);
-    attn_bwd_kernel<MODE><<<grid, kBwdThreads, smem, st>>>(mq, mk, mv, mdo, a);
+    attn_bwd_kernel<MODE><<<grid, kBwdThreads, smem, st>>>(mq, mk, mv, mdo, mc, a);
     MDT_CHECK_CUDA(cudaGetLastError());
     return MDT_OK;
 }
@@ -432,12 +463,15 @@ extern "C" int mdt_biased_attn_bwd(const void *q, const void *k, const void *v, 
     a.dk_sb = g->k_stride_b, a.dk_st = g->k_stride_t, a.dk_sh = g->k_stride_h;
     a.dv_sb = g->v_stride_b, a.dv_st = g->v_stride_t, a.dv_sh = g->v_stride_h;
     a.grad_bias = grad_bias, a.grad_lut = grad_lut;
+    CUtensorMap mc = mq;  // only read by the code mode
+    if (code)
+        if (int rc2 = make_tensor_map_u8_2d(&mc, code, (uint64_t)code_pitch, (uint64_t)B * T, (uint64_t)code_pitch, kTile)) return rc2;
     int rc;
     switch (bias_mode(bias, bias_dtype, code)) {
-        case kBiasNone: rc = launch_bwd<kBiasNone>(mq, mk, mv, mdo, a, st); break;
-        case kBiasF32: rc = launch_bwd<kBiasF32>(mq, mk, mv, mdo, a, st); break;
-        case kBiasBF16: rc = launch_bwd<kBiasBF16>(mq, mk, mv, mdo, a, st); break;
-        default: rc = launch_bwd<kBiasCode>(mq, mk, mv, mdo, a, st); break;
+        case kBiasNone: rc = launch_bwd<kBiasNone>(mq, mk, mv, mdo, mc, a, st); break;
+        case kBiasF32: rc = launch_bwd<kBiasF32>(mq, mk, mv, mdo, mc, a, st); break;
+        case kBiasBF16: rc = launch_bwd<kBiasBF16>(mq, mk, mv, mdo, mc, a, st); break;
+        default: rc = launch_bwd<kBiasCode>(mq, mk, mv, mdo, mc, a, st); break;
     }
     if (rc) return rc;
     {
