@@ -88,6 +88,7 @@ def main():
     ap.add_argument("--fusion-shapes", action="store_true", help="also (B'=4096,T=104) text and (410,201) image shapes")
     ap.add_argument("--no-flush", action="store_true")
     ap.add_argument("--json", default=None)
+    ap.add_argument("--no-lut-grad", action="store_true", help="code mode without the LUT gradient (no binning)")
     a = ap.parse_args()
     burst, sustained, src = peaks()
     flush = None if a.no_flush else torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
@@ -97,9 +98,11 @@ def main():
     rows = []
     for B, H, T in shapes:
         q, k, v, kw = make_inputs(B, H, T, a.mode)
+        if a.no_lut_grad and "lut" in kw:
+            kw["lut"] = kw["lut"].detach()
         o = ops.biased_attention(q, k, v, **kw)
         go = torch.randn_like(o)
-        inputs = [q, k, v] + [t for t in (kw.get("lut"), kw.get("bias")) if t is not None]
+        inputs = [q, k, v] + [t for t in (kw.get("lut"), kw.get("bias")) if t is not None and t.requires_grad]
 
         def fwd():
             with torch.no_grad():

@@ -110,7 +110,8 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
     __shared__ uint32_t tmem_base_s;
     __shared__ __align__(16) float s_nlse[2][128];   // -lse * log2(e); -inf for queries >= T
     __shared__ __align__(16) float s_delta[2][128];
-    __shared__ float s_lut[256];
+    __shared__ float s_lut[256];        // materialised-free modes: lut * log2(e), -inf for MDT_CODE_MASKED
+    __shared__ uint8_t s_bin[256];      // bias code -> gradient bin
 
     const int tid = threadIdx.x, warp = tid >> 5;
     const int r = tid & 127, half = tid >> 7;  // key row inside the tile, which half of the query columns
@@ -167,7 +168,8 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
         tmem_relinquish();
     }
     if (MODE == kBiasCode) {
-        s_lut[tid] = (tid == MDT_CODE_MASKED) ? neg_inf() : a.lut[(size_t)h * 256 + tid];
+        s_lut[tid] = (tid == MDT_CODE_MASKED) ? neg_inf() : a.lut[(size_t)h * 256 + tid] * kLog2e;
+        s_bin[tid] = tid == MDT_CODE_VIRTUAL ? (uint8_t)(kBins - 1) : (uint8_t)min(tid, kBins - 2);
         if (want_glut)
             for (int c = 0; c < kBins; ++c) bins[c * kBwdThreads + tid] = 0.f;
     }
@@ -232,6 +234,77 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
                     const uint32_t off = (cc >> 1) * 16384 + sw128_offset(r, (cc & 1) * 4 + u);
                     *reinterpret_cast<uint4 *>(sPt + off) = make_uint4(0, 0, 0, 0);
                     *reinterpret_cast<uint4 *>(sdSt + off) = make_uint4(0, 0, 0, 0);
+                }
+                continue;
+            }
+            if (MODE == kBiasCode || MODE == kBiasNone) {
+                // ---- lean path.  No per-element validity tests: queries past T carry -lse = -inf (p = 0), keys past
+                // T or padded zero the whole thread, rows of the next batch inside the tile are killed by the same -inf.
+                float st[32], dp[32];
+                tmem_ld_32x32(lane_base + cS + cc * 32, reinterpret_cast<uint32_t *>(st));   // .sync.aligned: whole warp
+                tmem_ld_32x32(lane_base + cDP + cc * 32, reinterpret_cast<uint32_t *>(dp));
+                tmem_wait_ld();
+                if (key_ok) {
+                    const uint32_t cbase = smem_u32(sCode + (i & 1) * 16384) + cc * 4096 + (r & 15);
+                    const uint32_t rchunk = (uint32_t)(r >> 4) << 4;
+                    const uint32_t lut_base = smem_u32(s_lut), bin_base = smem_u32(s_bin);
+                    float *my_bins = bins + tid;
+                    uint32_t bin_of[32];
+#pragma unroll
+                    for (int i2 = 0; i2 < 32; i2 += 4) {
+                        const float4 n4 = *reinterpret_cast<const float4 *>(nl + cc * 32 + i2);
+                        const float4 d4 = *reinterpret_cast<const float4 *>(dl + cc * 32 + i2);
+                        const float nn[4] = {n4.x, n4.y, n4.z, n4.w}, dd[4] = {d4.x, d4.y, d4.z, d4.w};
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            const int e = i2 + u;
+                            float x;
+                            uint32_t c = 0;
+                            if (MODE == kBiasCode) {
+                                // byte (query cc*32+e, key r) of the [query][key] tile: 128-byte rows, 16-byte chunks XOR-swizzled by row & 7
+                                asm("ld.shared.u8 %0, [%1];" : "=r"(c) : "r"(cbase + e * 128 + (rchunk ^ ((e & 7) << 4))));
+                                x = fmaf(st[e], kLog2e, lds_f32(lut_base + c * 4));
+                            } else {
+                                x = st[e] * kLog2e;
+                            }
+                            const float p = ex2(x + nn[u]);
+                            const float ds = p * (dp[e] - dd[u]);
+                            st[e] = p;
+                            dp[e] = ds;
+                            if (MODE == kBiasCode && want_glut) asm("ld.shared.u8 %0, [%1];" : "=r"(bin_of[e]) : "r"(bin_base + c));
+                        }
+                    }
+                    // ---- LUT gradient: per-thread bins [bin][tid] (conflict free, no atomics; masked codes carry dS = 0).
+                    // The read-modify-writes of one thread form a dependent chain, so they go in pairs: both loads
+                    // first, and when the two elements share a bin the second store carries both addends.
+                    if (MODE == kBiasCode && want_glut) {
+#pragma unroll
+                        for (int e = 0; e < 32; e += 2) {
+                            float *p0 = my_bins + bin_of[e] * kBwdThreads, *p1 = my_bins + bin_of[e + 1] * kBwdThreads;
+                            const float a0 = *p0 + dp[e];
+                            const float a1 = (bin_of[e] == bin_of[e + 1] ? a0 : *p1) + dp[e + 1];
+                            *p0 = a0;
+                            *p1 = a1;
+                        }
+                    }
+                } else {
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) st[e] = dp[e] = 0.f;
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    uint4 vp, vd;
+                    vp.x = pack_bf16x2(st[u * 8 + 0], st[u * 8 + 1]);
+                    vp.y = pack_bf16x2(st[u * 8 + 2], st[u * 8 + 3]);
+                    vp.z = pack_bf16x2(st[u * 8 + 4], st[u * 8 + 5]);
+                    vp.w = pack_bf16x2(st[u * 8 + 6], st[u * 8 + 7]);
+                    vd.x = pack_bf16x2(dp[u * 8 + 0], dp[u * 8 + 1]);
+                    vd.y = pack_bf16x2(dp[u * 8 + 2], dp[u * 8 + 3]);
+                    vd.z = pack_bf16x2(dp[u * 8 + 4], dp[u * 8 + 5]);
+                    vd.w = pack_bf16x2(dp[u * 8 + 6], dp[u * 8 + 7]);
+                    const uint32_t off = (cc >> 1) * 16384 + sw128_offset(r, (cc & 1) * 4 + u);
+                    *reinterpret_cast<uint4 *>(sPt + off) = vp;
+                    *reinterpret_cast<uint4 *>(sdSt + off) = vd;
                 }
                 continue;
             }
