@@ -184,6 +184,7 @@ def build_model(device):
     torch.manual_seed(0)
     args = published_args(dropout=DROPOUTS[0], attention_dropout=DROPOUTS[1], act_dropout=DROPOUTS[2])
     model = GraphormerModel.build_model(args, None).to(device=device, dtype=torch.bfloat16)
+    model.encoder.graph_encoder.pack_text = os.environ.get("MDT_PACK_TEXT", "1") != "0"   # SURVEY 8f N1 (see config.text)
     crit = GraphPredictionNodeCrossEntropy(None, args.positive_weight, args.negative_weight).to(device)
     return args, model, crit
 
@@ -301,6 +302,8 @@ def run_b200(args):
                    "model": "published run_train.sh 8 4 5 2 2: 8 fusion layers (stacks of 2), 10 executed graph layers, nb=4, "
                             "spatial_pos_max=5, freeze_initial_encoders, AdamW fp32 master weights, update_freq 1",
                    "dropout": {"dropout": DROPOUTS[0], "attention_dropout": DROPOUTS[1], "act_dropout": DROPOUTS[2]},
+                   "text": "fusion-layer BERT blocks on packed (unpadded) tokens: padding tokens (46 % of the batch) are not computed; "
+                           "logits / loss / gradients equal the padded path (tests/test_gpu_modules.py), MDT_PACK_TEXT=0 restores it",
                    "note": "graph-layer attention dropout is 0 (published 0.3): in-kernel dropout not built yet",
                    "l2": "working set per step (activations, weights) >> 126 MB L2; batches cycle through a pool",
                    "parallelism": f"dp{world}", "peak_mem_gib": round(peak_mem, 1)},

@@ -176,6 +176,25 @@ int mdt_gather_rows(const void *src, int64_t src_pitch, const int32_t *index, in
 int mdt_scatter_rows(const void *src, int64_t src_pitch, const int32_t *index, int n_rows, int row_elems,
                      int dtype, void *dst, int64_t dst_pitch, mdt_stream_t stream);
 
+/* ------------------------------------------------------------------------------------
+ * N2  dense -> dropout -> + residual -> LayerNorm block tail, one pass each way
+ *     (Hugging Face BertSelfOutput / BertOutput inside the fusion layers, mDT/src/modules/multi_graphormer_fusion_layer.py:105-149;
+ *      mDT/src/modules/graphormer_graph_encoder_layer.py:127-130,139-141)
+ *   forward : z = dropout_p(x) + residual (residual may be null);  y = LayerNorm(z) * gamma + beta
+ *             x, residual, gamma, beta, y, z: bf16 [rows, C] / [C];  mean, rstd: f32 [rows];  C in {256,512,768,1024}
+ *             z (the rounded pre-norm sum) is saved for the backward; it may be null only without residual and
+ *             dropout (then the backward is given x as z).  The keep mask is a counter hash of (seed, element
+ *             index): it is never stored, the backward regenerates it from the same seed.
+ *   backward: dres = d z (null to skip), dx = keep * d z / (1 - p) (null to skip), dgamma / dbeta f32 [C] are
+ *             ACCUMULATED into (the caller zeroes them).
+ * ------------------------------------------------------------------------------------ */
+int mdt_dropout_add_ln_fwd(const void *x, const void *residual, const void *gamma, const void *beta, void *y, void *z,
+                           float *mean, float *rstd, int64_t rows, int C, float p, uint64_t seed, float eps,
+                           mdt_stream_t stream);
+int mdt_dropout_add_ln_bwd(const void *dy, const void *z, const float *mean, const float *rstd, const void *gamma,
+                           void *dx, void *dres, float *dgamma, float *dbeta, int64_t rows, int C, float p,
+                           uint64_t seed, mdt_stream_t stream);
+
 /* Self-test of the tcgen05 building blocks (shared-memory descriptor layouts, TMA 128-byte
  * swizzle, TMEM read-back); called by tests/ only.  All operands bf16, row major:
  *   d1[128,128] = a[128,64] * b[128,64]^T          (A and B K-major, both via TMA)

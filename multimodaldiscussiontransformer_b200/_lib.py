@@ -9,7 +9,7 @@ from __future__ import annotations
 
 import ctypes
 import os
-from ctypes import POINTER, Structure, c_char_p, c_int, c_int32, c_int64, c_void_p
+from ctypes import POINTER, Structure, c_char_p, c_float, c_int, c_int32, c_int64, c_uint64, c_void_p
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libmdt_b200.so")
@@ -52,6 +52,10 @@ SIGNATURES = {
                                      c_void_p, c_void_p, c_void_p, c_void_p]),
     "mdt_gather_rows": (c_int, [c_void_p, c_int64, c_void_p, c_int, c_int, c_int, c_void_p, c_int64, c_void_p]),
     "mdt_scatter_rows": (c_int, [c_void_p, c_int64, c_void_p, c_int, c_int, c_int, c_void_p, c_int64, c_void_p]),
+    "mdt_dropout_add_ln_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64,
+                                       c_int, c_float, c_uint64, c_float, c_void_p]),
+    "mdt_dropout_add_ln_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                       c_int64, c_int, c_float, c_uint64, c_void_p]),
     "mdt_umma_selftest": (c_int, [c_void_p] * 10),
 }
 
@@ -80,7 +84,8 @@ def load():
 CALLS: dict = {}
 KERNELS_PER_CALL = {"mdt_apsp_batched": 1, "mdt_gen_edge_input": 1, "mdt_collate_graphs": 2, "mdt_attn_bias_fwd": 1,
                     "mdt_attn_bias_bwd": 1, "mdt_biased_attn_fwd": 1, "mdt_biased_attn_bwd": 3, "mdt_node_feature_fwd": 1,
-                    "mdt_node_feature_bwd": 1, "mdt_gather_rows": 1, "mdt_scatter_rows": 1, "mdt_umma_selftest": 1}
+                    "mdt_node_feature_bwd": 1, "mdt_gather_rows": 1, "mdt_scatter_rows": 1, "mdt_umma_selftest": 1, "mdt_dropout_add_ln_fwd": 1,
+                    "mdt_dropout_add_ln_bwd": 1}
 
 
 def kernel_launches() -> int:

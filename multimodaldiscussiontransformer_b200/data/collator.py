@@ -97,13 +97,19 @@ class HostBatch:
         node_index = np.concatenate([b * N + np.arange(n, dtype=np.int32) for b, n in enumerate(ns)])
         has_img = np.concatenate([_np(it.x_image_index).reshape(-1) for it in items]).astype(bool)
         img_rows = np.nonzero(has_img)[0].astype(np.int32)
-        # int32 staging buffer: [src | dst | offsets | n_nodes | node_index | image rows | idx]
-        ints = torch.empty(2 * E + (B + 1) + B + n_real + len(img_rows) + B, dtype=torch.int32)
+        # real text tokens per comment (attention_mask is a prefix of ones for tokenizer output): lets the fusion
+        # layers run on packed tokens without a device->host sync
+        att_all = np.concatenate([_np(it.x["attention_mask"]).reshape(n, -1) for it, n in zip(items, ns)]) != 0
+        text_lens = att_all.sum(1).astype(np.int32)
+        self.text_prefix = bool((att_all == (np.arange(att_all.shape[1])[None, :] < text_lens[:, None])).all())
+        self.text_tokens, self.text_max = int(text_lens.sum()), int(text_lens.max()) if n_real else 0
+        # int32 staging buffer: [src | dst | offsets | n_nodes | node_index | image rows | idx | text lengths]
+        ints = torch.empty(2 * E + (B + 1) + B + n_real + len(img_rows) + B + n_real, dtype=torch.int32)
         iv = ints.numpy()
         o = 0
         for arr in (np.concatenate(srcs) if E else np.zeros(0, np.int32), np.concatenate(dsts) if E else np.zeros(0, np.int32),
                     np.asarray(offs, np.int32), np.asarray(ns, np.int32), node_index, img_rows,
-                    np.asarray([int(it.idx) for it in items], np.int32)):
+                    np.asarray([int(it.idx) for it in items], np.int32), text_lens):
             iv[o:o + len(arr)] = arr
             o += len(arr)
         self.n_img_rows = len(img_rows)
@@ -158,6 +164,8 @@ def collate_device(raw: RawBatch, spatial_pos_max: int = 10) -> Dict[str, Any]:
     img_rows = ints[o:o + hb.n_img_rows]
     o += hb.n_img_rows
     idx = ints[o:o + B]
+    o += B
+    text_lens = ints[o:o + n_real]
     spatial_pos = torch.empty((B, N, N), dtype=torch.int32, device=device)
     attn_bias = torch.empty((B, T, T), dtype=torch.float32, device=device)
     in_degree = torch.empty((B, N), dtype=torch.int64, device=device)
@@ -194,6 +202,8 @@ def collate_device(raw: RawBatch, spatial_pos_max: int = 10) -> Dict[str, Any]:
         n_nodes=n_d,
         x_nodes=text_d,
         x_image_rows=img_rows,
+        # (lengths on the device, total and longest on the host) when every attention_mask is a prefix of ones
+        x_text_pack=(text_lens, hb.text_tokens, hb.text_max) if hb.text_prefix else None,
     )
     if hb.has_y_mask:
         out["y_mask"] = t["flags"][1]                                       # dataset.py:210-213

@@ -11,6 +11,8 @@ from typing import Optional
 import torch
 import torch.nn as nn
 
+from .. import ops
+
 
 def _first(out):
     return out[0] if isinstance(out, (tuple, list)) else out
@@ -23,6 +25,78 @@ def image_rows(x_image_indexes: Optional[torch.Tensor]) -> Optional[torch.Tensor
     if x_image_indexes.dtype == torch.bool:
         return torch.nonzero(x_image_indexes).squeeze(1)
     return x_image_indexes.long()
+
+
+class TextPack:
+    """Packed (unpadded) layout of the BERT side of the fusion layers.
+
+    Every comment i is one sequence ``[nb bottleneck slots | len_i real text tokens]``; the sequences are laid end
+    to end in one ``[total, C]`` buffer, so the layer GEMMs, LayerNorms, GELUs and the attention only touch real
+    tokens (padding is ~46 % of a HatefulDiscussions-shaped batch).  Built on the device from the per-comment
+    lengths without a host sync: the totals come from the host side of the collator.
+    Padding tokens never influence a real token in the reference either (additive key mask,
+    multigraphormer_graph_encoder.py:341-354), so logits, loss and gradients are unchanged; the hidden states
+    returned *at padding positions* are zeros instead of the reference's don't-care values.
+    """
+
+    def __init__(self, text_lens: torch.Tensor, text_tokens: int, text_max: int, nb: int, L: int):
+        dev = text_lens.device
+        n = text_lens.numel()
+        lens = text_lens.long()
+        self.nb, self.L, self.n = nb, L, n
+        self.total = text_tokens + nb * n
+        self.max_seqlen = text_max + nb
+        cu = torch.zeros(n + 1, dtype=torch.int64, device=dev)
+        cu[1:] = torch.cumsum(lens + nb, 0)
+        self.cu_seqlens = cu.to(torch.int32)
+        seq = torch.repeat_interleave(torch.arange(n, device=dev), lens, output_size=text_tokens)
+        cu_text = torch.cumsum(lens, 0) - lens
+        pos = torch.arange(text_tokens, device=dev) - cu_text[seq]
+        self.text_rows = cu[seq] + nb + pos                       # packed row of every real text token
+        self.padded_rows = seq * L + pos                          # its row in the padded [n * L] layout
+        self.bn_rows = (cu[:-1, None] + torch.arange(nb, device=dev)[None, :]).reshape(-1)  # [n * nb]
+
+    def pack(self, text_padded: torch.Tensor, bottle_neck: torch.Tensor) -> torch.Tensor:
+        C = text_padded.shape[-1]
+        x = text_padded.new_empty(self.total, C)
+        x = x.index_copy(0, self.text_rows, text_padded.reshape(-1, C).index_select(0, self.padded_rows))
+        return x.index_copy(0, self.bn_rows, bottle_neck.reshape(-1, C))
+
+    def unpack_text(self, x: torch.Tensor) -> torch.Tensor:
+        C = x.shape[-1]
+        out = x.new_zeros(self.n * self.L, C)
+        return out.index_copy(0, self.padded_rows, x.index_select(0, self.text_rows)).view(self.n, self.L, C)
+
+
+_FLASH = None
+
+
+def _varlen_attention(q, k, v, pack: "TextPack", dropout_p: float):
+    """Self-attention over the packed sequences: ``[total, H, d]`` -> ``[total, H, d]`` (library kernel: flash-attn)."""
+    global _FLASH
+    if _FLASH is None:
+        from flash_attn import flash_attn_varlen_func
+        _FLASH = flash_attn_varlen_func
+    return _FLASH(q, k, v, pack.cu_seqlens, pack.cu_seqlens, pack.max_seqlen, pack.max_seqlen, dropout_p=dropout_p)
+
+
+def packed_bert_layer(layer, x: torch.Tensor, pack: "TextPack") -> torch.Tensor:
+    """Hugging Face ``BertLayer`` arithmetic (post-LN block, same parameters, same dropout rates) on packed tokens."""
+    att, sa = layer.attention, layer.attention.self
+    H = sa.num_attention_heads
+    d = x.shape[-1] // H
+    q, k, v = (f(x).view(-1, H, d) for f in (sa.query, sa.key, sa.value))
+    ctx = _varlen_attention(q, k, v, pack, sa.dropout.p if layer.training else 0.0).reshape(x.shape)
+    if x.dtype == torch.bfloat16 and x.shape[-1] in (256, 512, 768, 1024):
+        # dense -> dropout -> + residual -> LayerNorm tails in one pass each way (libmdt_b200, csrc/layernorm.cu)
+        ln1, ln2 = att.output.LayerNorm, layer.output.LayerNorm
+        h = ops.dropout_add_layer_norm(att.output.dense(ctx), x, ln1.weight, ln1.bias, att.output.dropout.p, layer.training, ln1.eps)
+        inter = layer.intermediate(h)
+        return ops.dropout_add_layer_norm(layer.output.dense(inter), h, ln2.weight, ln2.bias, layer.output.dropout.p,
+                                          layer.training, ln2.eps)
+    h = att.output.LayerNorm(att.output.dropout(att.output.dense(ctx)) + x)
+    inter = layer.intermediate(h)
+    return layer.output.LayerNorm(layer.output.dropout(layer.output.dense(inter)) + h)
 
 
 class GraphFusionLayer(nn.Module):
@@ -62,6 +136,24 @@ class GraphFusionLayer(nn.Module):
         return bert_hidden_output, vit_hidden_output, bottle_neck_output
 
 
+    def forward_packed(self, x_packed, vit_hidden_states, bottle_neck, pack: TextPack, x_image_indexes=None):
+        """Same block on the packed layout: ``x_packed`` already holds the text tokens; the bottleneck slots are
+        (re)written from ``bottle_neck`` and read back after the BERT layer."""
+        nb = self.num_bottle_neck_tokens
+        C = x_packed.shape[-1]
+        x_packed = packed_bert_layer(self.bert_encoder, x_packed.index_copy(0, pack.bn_rows, bottle_neck.reshape(-1, C)), pack)
+        bottle_neck_output = x_packed.index_select(0, pack.bn_rows).view(-1, nb, C)
+        if vit_hidden_states is not None:
+            rows = image_rows(x_image_indexes)
+            vit_out = self.vit_forward(torch.cat([bottle_neck.index_select(0, rows), vit_hidden_states], dim=1))
+            vit_hidden_output = vit_out[:, nb:]
+            mixed = (vit_out[:, :nb] + bottle_neck_output.index_select(0, rows)) / 2
+            bottle_neck_output = bottle_neck_output.index_copy(0, rows, mixed)
+        else:
+            vit_hidden_output = None
+        return x_packed, vit_hidden_output, bottle_neck_output
+
+
 class GraphFusionStack(nn.Module):
     def __init__(self, bert_layers, vit_layers, num_bottle_neck_tokens, use_projection=False) -> None:
         super().__init__()
@@ -74,3 +166,9 @@ class GraphFusionStack(nn.Module):
             bert_hidden_states, vit_hidden_states, bottle_neck = f_layer(
                 bert_hidden_states, vit_hidden_states, bottle_neck, bert_attention_mask, rows)
         return bert_hidden_states, vit_hidden_states, bottle_neck
+
+    def forward_packed(self, x_packed, vit_hidden_states, bottle_neck, pack: TextPack, x_image_indexes=None):
+        rows = image_rows(x_image_indexes)
+        for f_layer in self.fusion_layers:
+            x_packed, vit_hidden_states, bottle_neck = f_layer.forward_packed(x_packed, vit_hidden_states, bottle_neck, pack, rows)
+        return x_packed, vit_hidden_states, bottle_neck

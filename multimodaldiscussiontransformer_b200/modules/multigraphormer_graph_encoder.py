@@ -17,7 +17,7 @@ from .. import ops
 from ._fairseq_compat import FairseqDropout, LayerNorm
 from .graphormer_graph_encoder_layer import GraphEncoderStack
 from .graphormer_layers import GraphAttnBias, GraphNodeFeature
-from .multi_graphormer_fusion_layer import GraphFusionStack, image_rows
+from .multi_graphormer_fusion_layer import GraphFusionStack, TextPack, image_rows
 from .multihead_attention import MultiheadAttention
 
 logger = logging.getLogger(__name__)
@@ -50,6 +50,9 @@ def _chunks(xs, k):
 class MultiGraphormerGraphEncoder(nn.Module):
     #: use the in-kernel bias synthesis (code + lut) when the batch carries ``bias_code``
     fused_bias = True
+    #: run the BERT side of the fusion layers on packed (unpadded) tokens when the batch carries ``x_text_pack`` and
+    #: the model computes in bf16/fp16; hidden states at padding positions come back as zeros
+    pack_text = False
     #: try the local Hugging Face cache for the pretrained trunks before falling back to config init
     pretrained = False
 
@@ -205,7 +208,14 @@ class MultiGraphormerGraphEncoder(nn.Module):
         bottle_neck = self.bottle_neck.weight.to(dtype).unsqueeze(0).repeat(n_real, 1, 1)                    # :339
         am = torch.cat([att.new_ones(n_real, self.num_bottle_neck), att], dim=1)
         ext_mask = ((1.0 - am[:, None, None, :].to(torch.float32)) * torch.finfo(torch.half).min).to(dtype)  # :341-354
-        bert_output, vit_output, bottle_neck = self.fusion_layers[0](bert_output, vit_output, bottle_neck, ext_mask, img_rows)
+        pack = None
+        if self.pack_text and batched_data.get("x_text_pack") is not None and dtype in (torch.bfloat16, torch.float16):
+            lens, total, longest = batched_data["x_text_pack"]
+            pack = TextPack(lens, total, longest, self.num_bottle_neck, bert_output.shape[1])
+            x_text = pack.pack(bert_output, bottle_neck)
+            x_text, vit_output, bottle_neck = self.fusion_layers[0].forward_packed(x_text, vit_output, bottle_neck, pack, img_rows)
+        else:
+            bert_output, vit_output, bottle_neck = self.fusion_layers[0](bert_output, vit_output, bottle_neck, ext_mask, img_rows)
 
         # node-major -> padded [B,N,C]                                                                   :363-371
         graph_data = ops.scatter_rows(bottle_neck.new_zeros(B * N, 768), bottle_neck[:, 0, :], node_rows).view(B, N, 768)
@@ -230,9 +240,14 @@ class MultiGraphormerGraphEncoder(nn.Module):
             x, _ = g_layer(x, self_attn_padding_mask=padding_mask, self_attn_mask=attn_mask, self_attn_bias=attn_bias)
             xf = x.reshape(T * B, self.embedding_dim)
             bottle_neck = torch.cat([ops.gather_rows(xf, tb_rows).unsqueeze(1), bottle_neck[:, 1:]], dim=1)   # :425
-            bert_output, vit_output, bottle_neck = f_layer(bert_output, vit_output, bottle_neck, ext_mask, img_rows)
+            if pack is not None:
+                x_text, vit_output, bottle_neck = f_layer.forward_packed(x_text, vit_output, bottle_neck, pack, img_rows)
+            else:
+                bert_output, vit_output, bottle_neck = f_layer(bert_output, vit_output, bottle_neck, ext_mask, img_rows)
             x = ops.scatter_rows(xf, bottle_neck[:, 0, :], tb_rows).view(T, B, self.embedding_dim)           # :435
             if not last_state_only:
                 inner_states.append(x)
         x, _ = self.layers[-1](x, self_attn_padding_mask=padding_mask, self_attn_mask=attn_mask, self_attn_bias=attn_bias)
+        if pack is not None:
+            bert_output = pack.unpack_text(x_text)
         return bert_output, bottle_neck, x[0, :, :]

@@ -301,3 +301,67 @@ def biased_attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, bias: Op
     if code is not None and lut is None:
         raise ValueError("code needs lut")
     return _BiasedAttention.apply(q, k, v, bias, code, lut, key_padding_mask)
+
+
+# ------------------------------------------------------------------------------------------
+# N2  dense -> dropout -> + residual -> LayerNorm tail of the post-LN blocks, one pass each way
+#     (HF BertSelfOutput / BertOutput in the fusion layers; graphormer_graph_encoder_layer.py:127-130,139-141)
+# ------------------------------------------------------------------------------------------
+class _DropoutAddLayerNorm(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, residual, weight, bias, p, eps, seed):
+        _require_cuda(x, residual, weight, bias)
+        lib = _lib.load()
+        C = x.shape[-1]
+        x2 = x.reshape(-1, C).contiguous()
+        r2 = residual.reshape(-1, C).contiguous() if residual is not None else None
+        rows = x2.shape[0]
+        y = torch.empty_like(x2)
+        need_z = r2 is not None or p > 0.0
+        z = torch.empty_like(x2) if need_z else None
+        mean = torch.empty(rows, dtype=torch.float32, device=x.device)
+        rstd = torch.empty(rows, dtype=torch.float32, device=x.device)
+        w, b = weight.detach().contiguous(), bias.detach().contiguous()
+        with torch.cuda.device(x.device):
+            _lib.check(lib.mdt_dropout_add_ln_fwd(_lib.ptr(x2), _lib.ptr(r2), _lib.ptr(w), _lib.ptr(b), _lib.ptr(y), _lib.ptr(z),
+                                                  _lib.ptr(mean), _lib.ptr(rstd), rows, C, float(p), int(seed), float(eps),
+                                                  _lib.stream()), "mdt_dropout_add_ln_fwd")
+        ctx.save_for_backward(z if need_z else x2, mean, rstd, w)
+        ctx.meta = (float(p), int(seed), x.shape, residual is not None, weight.dtype)
+        return y.view(x.shape)
+
+    @staticmethod
+    def backward(ctx, gy):
+        z, mean, rstd, w = ctx.saved_tensors
+        p, seed, shape, has_res, wdtype = ctx.meta
+        lib = _lib.load()
+        C = shape[-1]
+        gy2 = gy.reshape(-1, C).contiguous()
+        rows = gy2.shape[0]
+        need_dx = ctx.needs_input_grad[0]
+        need_dres = has_res and ctx.needs_input_grad[1]
+        # without dropout d x == d residual: one tensor serves both
+        share = p == 0.0 and need_dx and need_dres
+        dres = torch.empty_like(gy2) if (need_dres or (share and need_dx)) else None
+        dx = torch.empty_like(gy2) if (need_dx and not share) else None
+        dgamma = torch.zeros(C, dtype=torch.float32, device=gy.device)
+        dbeta = torch.zeros(C, dtype=torch.float32, device=gy.device)
+        if dx is None and dres is None:
+            dres = torch.empty_like(gy2)
+        with torch.cuda.device(gy.device):
+            _lib.check(lib.mdt_dropout_add_ln_bwd(_lib.ptr(gy2), _lib.ptr(z), _lib.ptr(mean), _lib.ptr(rstd), _lib.ptr(w),
+                                                  _lib.ptr(dx), _lib.ptr(dres), _lib.ptr(dgamma), _lib.ptr(dbeta), rows, C,
+                                                  float(p), int(seed), _lib.stream()), "mdt_dropout_add_ln_bwd")
+        g_x = (dres if share else dx).view(shape) if need_dx else None
+        g_res = dres.view(shape) if need_dres else None
+        return g_x, g_res, dgamma.to(wdtype), dbeta.to(wdtype), None, None, None
+
+
+def dropout_add_layer_norm(x, residual, weight, bias, p: float = 0.0, training: bool = False, eps: float = 1e-5):
+    """``LayerNorm(dropout(x, p) + residual)`` in one pass (bf16 tensors, C in {256, 512, 768, 1024}); ``residual`` may be
+    None.  The dropout mask is a counter hash seeded from torch's CPU generator (reproducible under manual_seed)."""
+    if x.dtype != torch.bfloat16:
+        raise RuntimeError("dropout_add_layer_norm: bf16 only (libmdt_b200 has no other LayerNorm path)")
+    p = float(p) if training else 0.0
+    seed = int(torch.randint(0, 2 ** 62, (1,)).item()) if p > 0.0 else 0
+    return _DropoutAddLayerNorm.apply(x, residual, weight, bias, p, eps, seed)

@@ -1,0 +1,89 @@
+"""GPU parity of the fused dropout + residual + LayerNorm kernels (csrc/layernorm.cu) against the plain PyTorch fp32
+formula ``LayerNorm(dropout(x) + residual)`` -- the tail of the post-LN blocks on the path (HF BertSelfOutput /
+BertOutput inside the fusion layers; graphormer_graph_encoder_layer.py:127-130,139-141).
+
+Tolerances: bf16 outputs ``<= 2e-2`` absolute on O(1) values; gradients ``<= 2e-2`` relative Frobenius (fp32 math inside,
+bf16 rounding of the saved pre-norm sum and of the outputs).
+"""
+
+from __future__ import annotations
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def rel(a, b):
+    return float((a.float() - b.float()).norm() / b.float().norm().clamp_min(1e-12))
+
+
+def reference(x, res, w, b, keep, scale, eps):
+    z = x.float() * keep * scale + (res.float() if res is not None else 0.0)
+    z = z.bfloat16().float()  # the kernel normalises the rounded sum it saves
+    return F.layer_norm(z, (x.shape[-1],), w.float(), b.float(), eps)
+
+
+@pytest.mark.parametrize("C", [256, 768, 1024])
+@pytest.mark.parametrize("rows", [1, 37, 5000])
+@pytest.mark.parametrize("with_res", [True, False])
+def test_add_layer_norm_no_dropout(C, rows, with_res):
+    from multimodaldiscussiontransformer_b200 import ops
+
+    g = torch.Generator(device="cuda").manual_seed(C + rows)
+    x = torch.randn(rows, C, device="cuda", generator=g).bfloat16().requires_grad_(True)
+    res = torch.randn(rows, C, device="cuda", generator=g).bfloat16().requires_grad_(True) if with_res else None
+    w = (1 + 0.1 * torch.randn(C, device="cuda", generator=g)).bfloat16().requires_grad_(True)
+    b = (0.1 * torch.randn(C, device="cuda", generator=g)).bfloat16().requires_grad_(True)
+    go = torch.randn(rows, C, device="cuda", generator=g).bfloat16()
+    y = ops.dropout_add_layer_norm(x, res, w, b, 0.3, training=False, eps=1e-12)
+    ins = [t for t in (x, res, w, b) if t is not None]
+    got = torch.autograd.grad(y, ins, go)
+    xr, rr, wr, br = (t.detach().float().requires_grad_(True) if t is not None else None for t in (x, res, w, b))
+    yr = reference(xr, rr, wr, br, 1.0, 1.0, 1e-12)
+    want = torch.autograd.grad(yr, [t for t in (xr, rr, wr, br) if t is not None], go.float())
+    assert float((y.float() - yr).abs().max()) <= 2e-2
+    for a, b_ in zip(got, want):
+        assert rel(a, b_) <= 2e-2
+
+
+@pytest.mark.parametrize("p", [0.1, 0.4])
+def test_dropout_add_layer_norm_training(p):
+    from multimodaldiscussiontransformer_b200 import ops
+
+    rows, C = 4096, 768
+    g = torch.Generator(device="cuda").manual_seed(7)
+    x = (torch.randn(rows, C, device="cuda", generator=g) + 3.0).bfloat16().requires_grad_(True)
+    res = torch.randn(rows, C, device="cuda", generator=g).bfloat16().requires_grad_(True)
+    w = (1 + 0.1 * torch.randn(C, device="cuda", generator=g)).bfloat16().requires_grad_(True)
+    b = (0.1 * torch.randn(C, device="cuda", generator=g)).bfloat16().requires_grad_(True)
+    go = torch.randn(rows, C, device="cuda", generator=g).bfloat16()
+    torch.manual_seed(123)
+    y = ops.dropout_add_layer_norm(x, res, w, b, p, training=True, eps=1e-12)
+    gx, gr, gw, gb = torch.autograd.grad(y, [x, res, w, b], go)
+    torch.manual_seed(123)
+    y2 = ops.dropout_add_layer_norm(x, res, w, b, p, training=True, eps=1e-12)
+    assert torch.equal(y, y2)                                    # same seed -> same mask
+    keep = (gx != 0).float()                                     # d x is exactly 0 where the element was dropped
+    assert abs(float(1 - keep.mean()) - p) < 5e-3                # drop rate
+    assert abs(float(keep[:, 0].mean()) - float(keep[:, C - 1].mean())) < 5e-2
+    xr, rr, wr, br = (t.detach().float().requires_grad_(True) for t in (x, res, w, b))
+    yr = reference(xr, rr, wr, br, keep, 1.0 / (1.0 - p), 1e-12)
+    want = torch.autograd.grad(yr, [xr, rr, wr, br], go.float())
+    assert float((y.float() - yr).abs().max()) <= 3e-2           # the forward used the very mask the backward regenerates
+    for a, b_ in zip((gx, gr, gw, gb), want):
+        assert rel(a, b_) <= 2e-2
+
+
+def test_layer_norm_rejects_other_dtypes_and_widths():
+    from multimodaldiscussiontransformer_b200 import ops
+
+    x = torch.randn(4, 768, device="cuda")
+    w = torch.ones(768, device="cuda")
+    with pytest.raises(RuntimeError):
+        ops.dropout_add_layer_norm(x, None, w, w)
+    xb = torch.randn(4, 640, device="cuda").bfloat16()
+    wb = torch.ones(640, device="cuda").bfloat16()
+    with pytest.raises(RuntimeError):
+        ops.dropout_add_layer_norm(xb, None, wb, wb)

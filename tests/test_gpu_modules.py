@@ -168,3 +168,38 @@ def test_reference_format_batch_matches_fast_path():
         b = enc(ref_fmt)
     for x, y in zip(a, b):
         assert float((x - y).abs().max()) <= 2e-2
+
+
+@pytest.mark.parametrize("name", ["tiny", "tiny_noimg"])
+def test_packed_text_fusion_matches_padded_path(name):
+    """the BERT side of the fusion layers on packed (unpadded) tokens gives the same logits, bottleneck
+    tokens, graph embedding, real-token hidden states and gradients as the padded Hugging Face path (bf16 model)."""
+    pytest.importorskip("flash_attn")
+    from multimodaldiscussiontransformer_b200.data.collator import collator
+
+    enc = build_encoder(name).to(torch.bfloat16)
+    items, spmax = cases.encoder_items(name)
+    batch = collator(items, spmax)
+    assert batch["x_text_pack"] is not None
+    res = {}
+    for packed in (False, True):
+        enc.pack_text = packed
+        enc.zero_grad(set_to_none=True)
+        text, bn, glob = enc(batch)
+        out_all = head(enc, text, bn)
+        loss, _ = orc.node_cross_entropy(out_all.float(), batch["y"], batch["y_mask"])
+        loss.backward()
+        res[packed] = dict(text=text.float(), bn=bn.float(), glob=glob.float(), out=out_all.float(), loss=float(loss),
+                           g_bn=enc.bottle_neck.weight.grad.float().clone(),
+                           g_q=enc.fusion_layers[0].fusion_layers[0].bert_encoder.attention.self.query.weight.grad.float().clone(),
+                           g_sp=enc.graph_attn_bias.spatial_pos_encoder.weight.grad.float().clone())
+    a, b = res[False], res[True]
+    att = batch["x_nodes"][2].bool()
+    assert float((a["out"] - b["out"]).abs().max()) <= 3e-2
+    assert float((a["bn"] - b["bn"]).abs().max()) <= 6e-2
+    assert float((a["glob"] - b["glob"]).abs().max()) <= 6e-2
+    assert float((a["text"][att] - b["text"][att]).abs().max()) <= 6e-2       # real tokens agree
+    assert float(b["text"][~att].abs().max()) == 0.0                            # padding positions come back as zeros
+    assert abs(a["loss"] - b["loss"]) <= 2e-2 * max(1.0, abs(a["loss"]))
+    for k in ("g_bn", "g_q", "g_sp"):
+        assert rel(b[k], a[k]) <= 8e-2, (k, rel(b[k], a[k]))
