@@ -8,6 +8,7 @@ from typing import Callable, Optional
 import torch
 import torch.nn as nn
 
+from .. import ops
 from ._fairseq_compat import FairseqDropout, LayerNorm, get_activation_fn, quant_noise
 from .multihead_attention import MultiheadAttention
 
@@ -54,17 +55,21 @@ class GraphormerGraphEncoderLayer(nn.Module):
             x = self.self_attn_layer_norm(x)
         x, attn = self.self_attn(query=x, key=x, value=x, attn_bias=self_attn_bias,
                                  key_padding_mask=self_attn_padding_mask, need_weights=False, attn_mask=self_attn_mask)
-        x = residual + self.dropout_module(x)
-        if not self.pre_layernorm:
-            x = self.self_attn_layer_norm(x)
+        x = self._add_norm(x, residual, self.self_attn_layer_norm)
         residual = x
         if self.pre_layernorm:
             x = self.final_layer_norm(x)
         x = self.activation_dropout_module(self.activation_fn(self.fc1(x)))
-        x = residual + self.dropout_module(self.fc2(x))
-        if not self.pre_layernorm:
-            x = self.final_layer_norm(x)
+        x = self._add_norm(self.fc2(x), residual, self.final_layer_norm)
         return x, attn
+
+    def _add_norm(self, x, residual, norm):
+        """``residual + dropout(x)`` followed by the post-LN (:127-130, :139-141); one fused pass on the bf16 CUDA path."""
+        if (not self.pre_layernorm and x.is_cuda and x.dtype == torch.bfloat16 and x.shape[-1] in (256, 512, 768, 1024)
+                and norm.weight is not None and norm.weight.dtype == torch.bfloat16):
+            return ops.dropout_add_layer_norm(x, residual, norm.weight, norm.bias, self.dropout_module.p, self.training, norm.eps)
+        x = residual + self.dropout_module(x)
+        return x if self.pre_layernorm else norm(x)
 
 
 class GraphEncoderStack(nn.Module):

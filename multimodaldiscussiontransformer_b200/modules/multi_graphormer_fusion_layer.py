@@ -99,11 +99,31 @@ def packed_bert_layer(layer, x: torch.Tensor, pack: "TextPack") -> torch.Tensor:
     return layer.output.LayerNorm(layer.output.dropout(layer.output.dense(inter)) + h)
 
 
+class FusedLayerNorm(nn.LayerNorm):
+    """``nn.LayerNorm`` (same parameters, same state-dict keys) whose bf16 CUDA forward / backward is the one-pass
+    kernel of csrc/layernorm.cu; anything else takes PyTorch's implementation."""
+
+    def forward(self, x):
+        if (x.is_cuda and x.dtype == torch.bfloat16 and len(self.normalized_shape) == 1 and self.weight is not None
+                and self.bias is not None and self.weight.dtype == torch.bfloat16
+                and self.normalized_shape[0] in (256, 512, 768, 1024)):
+            return ops.dropout_add_layer_norm(x, None, self.weight, self.bias, 0.0, False, self.eps)
+        return super().forward(x)
+
+
+def use_fused_layer_norms(module: nn.Module) -> nn.Module:
+    """Re-class every plain ``nn.LayerNorm`` below ``module`` (the ViT blocks are pre-LN: no residual to fuse)."""
+    for m in module.modules():
+        if type(m) is nn.LayerNorm:
+            m.__class__ = FusedLayerNorm
+    return module
+
+
 class GraphFusionLayer(nn.Module):
     def __init__(self, bert_layer, vit_layer, num_bottle_neck_tokens: int, use_projection: bool = False) -> None:
         super().__init__()
         self.bert_encoder = bert_layer
-        self.vit_encoder = vit_layer
+        self.vit_encoder = use_fused_layer_norms(vit_layer)
         self.gradient_checkpointing = False
         self.num_bottle_neck_tokens = num_bottle_neck_tokens
         if use_projection:  # constructed, never applied (multi_graphormer_fusion_layer.py:22-27)
