@@ -26,6 +26,7 @@ constexpr int kBwdThreads = 256;  // two warpgroups: each owns 64 of the 128 que
 
 struct BwdArgs {
     int B, H, T;
+    int Tmain;  // keys [0, Tmain) are this kernel's (all T queries); keys [Tmain, T) belong to attn_bwd_tail_k_kernel (attn_tail.cu)
     const void *bias;
     const uint8_t *code;
     int code_pitch;
@@ -119,7 +120,8 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
     const int T = a.T;
     const int k0 = blockIdx.x * kTile;
     const int key = k0 + r;
-    const bool key_ok = key < T && !(a.key_pad != nullptr && a.key_pad[(size_t)b * T + key] != 0);
+    const int Tm = a.Tmain;
+    const bool key_ok = key < Tm && !(a.key_pad != nullptr && a.key_pad[(size_t)b * T + key] != 0);
     const int nq = (T + kTile - 1) / kTile;
     const bool want_gbias = (MODE == kBiasF32 || MODE == kBiasBF16) && a.grad_bias != nullptr;
     const bool want_glut = MODE == kBiasCode && a.grad_lut != nullptr;
@@ -128,7 +130,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
     // A key tile without a single live key has dK = dV = 0 and adds nothing to dQ or the LUT gradient.
     // (The materialised-bias modes still have to write their d-bias zeros, so they take the long way.)
     if ((MODE == kBiasCode || MODE == kBiasNone) && !__syncthreads_or(key_ok ? 1 : 0)) {
-        if (key < T) {
+        if (key < Tm) {
             uint4 *pk = reinterpret_cast<uint4 *>(a.dk + (size_t)b * a.dk_sb + (size_t)key * a.dk_st + (size_t)h * a.dk_sh + half * 32);
             uint4 *pv = reinterpret_cast<uint4 *>(a.dv + (size_t)b * a.dv_sb + (size_t)key * a.dv_st + (size_t)h * a.dv_sh + half * 32);
 #pragma unroll
@@ -438,7 +440,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
         for (int which = 0; which < 2; ++which) {
             tmem_ld_32x32(lane_base + (which == 0 ? cDV : cDK) + half * 32, reinterpret_cast<uint32_t *>(acc));
             tmem_wait_ld();
-            if (key < T) {
+            if (key < Tm) {
                 __nv_bfloat16 *p = which == 0 ? a.dv + (size_t)b * a.dv_sb + (size_t)key * a.dv_st + (size_t)h * a.dv_sh
                                               : a.dk + (size_t)b * a.dk_sb + (size_t)key * a.dk_st + (size_t)h * a.dk_sh;
                 p += half * 32;
@@ -475,7 +477,7 @@ static int launch_bwd(const CUtensorMap &mq, const CUtensorMap &mk, const CUtens
         MDT_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         configured = smem;
     }
-    dim3 grid((a.T + kTile - 1) / kTile, a.H, a.B);
+    dim3 grid((a.Tmain + kTile - 1) / kTile, a.H, a.B);
     attn_bwd_kernel<MODE><<<grid, kBwdThreads, smem, st>>>(mq, mk, mv, mdo, mc, a);
     MDT_CHECK_CUDA(cudaGetLastError());
     return MDT_OK;
@@ -536,6 +538,8 @@ extern "C" int mdt_biased_attn_bwd(const void *q, const void *k, const void *v, 
     a.dk_sb = g->k_stride_b, a.dk_st = g->k_stride_t, a.dk_sh = g->k_stride_h;
     a.dv_sb = g->v_stride_b, a.dv_st = g->v_stride_t, a.dv_sh = g->v_stride_h;
     a.grad_bias = grad_bias, a.grad_lut = grad_lut;
+    const int mode = bias_mode(bias, bias_dtype, code);
+    a.Tmain = tail_split(T, mode == kBiasCode || mode == kBiasNone);
     CUtensorMap mc = mq;  // only read by the code mode
     if (code)
         if (int rc2 = make_tensor_map_u8_2d(&mc, code, (uint64_t)code_pitch, (uint64_t)B * T, (uint64_t)code_pitch, kTile)) return rc2;
@@ -547,6 +551,23 @@ extern "C" int mdt_biased_attn_bwd(const void *q, const void *k, const void *v, 
         default: rc = launch_bwd<kBiasCode>(mq, mk, mv, mdo, mc, a, st); break;
     }
     if (rc) return rc;
+    if (a.Tmain < T) {  // keys [Tmain, T) on CUDA cores (attn_tail.cu)
+        TailArgs t{};
+        t.B = B, t.H = H, t.T = T, t.Tmain = a.Tmain;
+        t.q = reinterpret_cast<const __nv_bfloat16 *>(q), t.k = reinterpret_cast<const __nv_bfloat16 *>(k);
+        t.v = reinterpret_cast<const __nv_bfloat16 *>(v);
+        t.q_sb = d->q_stride_b, t.q_st = d->q_stride_t, t.q_sh = d->q_stride_h;
+        t.k_sb = d->k_stride_b, t.k_st = d->k_stride_t, t.k_sh = d->k_stride_h;
+        t.v_sb = d->v_stride_b, t.v_st = d->v_stride_t, t.v_sh = d->v_stride_h;
+        t.code = code, t.code_pitch = code_pitch, t.lut = lut, t.key_pad = key_pad;
+        t.lse = const_cast<float *>(lse);
+        t.dout = reinterpret_cast<const __nv_bfloat16 *>(grad_out);
+        t.g_sb = g->o_stride_b, t.g_st = g->o_stride_t, t.g_sh = g->o_stride_h;
+        t.delta = delta, t.dq_accum = dq_accum, t.dk = a.dk, t.dv = a.dv;
+        t.dk_sb = a.dk_sb, t.dk_st = a.dk_st, t.dk_sh = a.dk_sh, t.dv_sb = a.dv_sb, t.dv_st = a.dv_st, t.dv_sh = a.dv_sh;
+        t.grad_lut = grad_lut;
+        if (int rc3 = launch_bwd_tails(t, st)) return rc3;
+    }
     {
         const int64_t n = (int64_t)B * H * T * 8;
         attn_dq_convert_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(dq_accum, B, H, T, reinterpret_cast<__nv_bfloat16 *>(dq),

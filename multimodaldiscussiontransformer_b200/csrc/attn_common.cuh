@@ -55,12 +55,38 @@ struct Fwd2Args {
     __nv_bfloat16 *out;
     int64_t o_sb, o_st, o_sh;
     float *lse;
+    int Tmain;                  // queries / keys processed: [0, Tmain) (= T; kept separate from the row pitch T)
     unsigned long long *trace;  // diagnostics: per-CTA globaltimer stamps (mdt_debug_attn_trace), else null
 };
 constexpr int kFwd3MaxT = 4096;  // the key-mask bitmap of a whole row lives in shared memory (attn_fwd3.cu)
 int launch_fwd3(const CUtensorMap &mq, const CUtensorMap &mk, const CUtensorMap &mv, const CUtensorMap &mc, const Fwd2Args &a,
                 cudaStream_t st);
 
+
+// tail keys of T = 128 k + r in the backward (attn_tail.cu): keys [Tmain, T) on CUDA cores
+constexpr int kTailMax = 8;
+inline int tail_split(int T, bool eligible) {  // -> Tmain
+    const int r = T % kTile;
+    return (eligible && T > kTile && r >= 1 && r <= kTailMax) ? T - r : T;
+}
+struct TailArgs {
+    int B, H, T, Tmain;
+    const __nv_bfloat16 *q, *k, *v;
+    int64_t q_sb, q_st, q_sh, k_sb, k_st, k_sh, v_sb, v_st, v_sh;
+    const uint8_t *code;
+    int code_pitch;
+    const float *lut;
+    const uint8_t *key_pad;
+    const float *lse;
+    const __nv_bfloat16 *dout;
+    int64_t g_sb, g_st, g_sh;
+    const float *delta;
+    float *dq_accum;
+    __nv_bfloat16 *dk, *dv;
+    int64_t dk_sb, dk_st, dk_sh, dv_sb, dv_st, dv_sh;
+    float *grad_lut;
+};
+int launch_bwd_tails(const TailArgs &a, cudaStream_t st);
 
 }  // namespace attn
 }  // namespace mdt

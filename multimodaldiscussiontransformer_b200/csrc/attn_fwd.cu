@@ -321,6 +321,7 @@ extern "C" int mdt_biased_attn_fwd(const void *q, const void *k, const void *v, 
         a2.B = d->B, a2.H = d->H, a2.T = d->T, a2.has_code = code != nullptr, a2.lut = lut, a2.key_pad = key_pad;
         a2.out = a.out, a2.o_sb = a.o_sb, a2.o_st = a.o_st, a2.o_sh = a.o_sh, a2.lse = lse;
         a2.trace = g_attn_trace;
+        a2.Tmain = d->T;
         return launch_fwd3(mq, mk, mv, mc, a2, st);
     }
     switch (mode) {

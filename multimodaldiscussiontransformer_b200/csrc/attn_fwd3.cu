@@ -75,10 +75,10 @@ __global__ void __launch_bounds__(kF3Threads, 1)
     F3Ctrl &ctl = *reinterpret_cast<F3Ctrl *>(smem + kF3Tiles);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int T = a.T, H = a.H;
-    const int nqp = (T + 2 * kTile - 1) / (2 * kTile);
+    const int T = a.T, H = a.H, Tm = a.Tmain;  // T: row pitch of lse / code / key_pad; Tm: queries and keys of this kernel
+    const int nqp = (Tm + 2 * kTile - 1) / (2 * kTile);
     const int n_items = a.B * H * nqp;
-    const int nkv_all = (T + kTile - 1) / kTile;
+    const int nkv_all = (Tm + kTile - 1) / kTile;
 
     if (tid == 0) {
         f3_trace(a, 0);
@@ -133,7 +133,7 @@ __global__ void __launch_bounds__(kF3Threads, 1)
 #pragma unroll
                     for (int i = 0; i < 32; ++i) {
                         const int kk = w * 32 + i;
-                        const bool masked = kk >= T || (kp != nullptr && kp[kk] != 0);
+                        const bool masked = kk >= Tm || (kp != nullptr && kp[kk] != 0);
                         bits |= (masked ? 1u : 0u) << i;
                     }
                     ctl.kmask[buf][w] = bits;
@@ -296,7 +296,7 @@ __global__ void __launch_bounds__(kF3Threads, 1)
             const int buf = n & 1;
             const F3Item it = f3_item(item, nqp, H);
             const int q = it.q_base + t * kTile + r;
-            const bool row_ok = q < T;
+            const bool row_ok = q < Tm;
             const bool warp_live = __any_sync(0xffffffffu, row_ok);  // warps past the end only keep the barriers moving
             mbar_wait(&ctl.aux_full[buf], (n >> 1) & 1);
             const int nkv = ctl.nkv[buf];
@@ -494,7 +494,7 @@ int launch_fwd3(const CUtensorMap &mq, const CUtensorMap &mk, const CUtensorMap 
         MDT_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd3_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kF3Smem));
         configured = true;
     }
-    const int nqp = (a.T + 2 * kTile - 1) / (2 * kTile);
+    const int nqp = (a.Tmain + 2 * kTile - 1) / (2 * kTile);
     const long long n_items = (long long)a.B * a.H * nqp;
     const int grid = (int)(n_items < (long long)num_sms() ? n_items : (long long)num_sms());
     if (a.has_code)
