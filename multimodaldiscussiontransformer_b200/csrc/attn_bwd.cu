@@ -230,7 +230,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
         const float *dl = s_delta[i & 1];
 #pragma unroll 1
         for (int cc = half * 2; cc < half * 2 + 2; ++cc) {
-            if (!warp_keys && !want_gbias) {  // 32 masked keys: P^T = dS^T = 0 for these rows
+            if ((!warp_keys || cc * 32 >= qvalid) && !want_gbias) {  // 32 masked keys, or 32 query columns past T: P^T = dS^T = 0
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
                     const uint32_t off = (cc >> 1) * 16384 + sw128_offset(r, (cc & 1) * 4 + u);
