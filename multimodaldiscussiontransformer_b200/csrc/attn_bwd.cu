@@ -107,7 +107,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
             *sdSt = smem + 131072;
     uint8_t *sCode = smem + kBwdSmemBase;                                           // 2 x 16 KB, only with codes
     float *bins = reinterpret_cast<float *>(smem + kBwdSmemBase + kBwdCodeBytes);  // [kBins][256], only with grad_lut
-    __shared__ __align__(8) uint64_t bar_kv, bar_qdo[2], bar_sp, bar_dq;
+    __shared__ __align__(8) uint64_t bar_kv, bar_qdo[2], bar_sp, bar_dq, bar_fin;
     __shared__ uint32_t tmem_base_s;
     __shared__ __align__(16) float s_nlse[2][128];   // -lse * log2(e); -inf for queries >= T
     __shared__ __align__(16) float s_delta[2][128];
@@ -158,6 +158,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
         mbar_init(&bar_qdo[1], 1);
         mbar_init(&bar_sp, 1);
         mbar_init(&bar_dq, 1);
+        mbar_init(&bar_fin, 1);
         fence_barrier_init();
         tma_prefetch_desc(&mq);
         tma_prefetch_desc(&mk);
@@ -219,10 +220,10 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
     for (int i = 0; i < nq; ++i) {
         const int q0 = i * kTile;
         const int qvalid = min(kTile, T - q0);
-        if (tid == 0 && i + 1 < nq) load_qdo(i + 1);  // buffer of tile i-1: its MMAs completed before bar_dq(i-1)
-        __syncwarp();
         mbar_wait(&bar_sp, i & 1);
         tc_fence_after();
+        // buffer of tile i-1: bar_sp(i) was committed after every MMA that read it (dV, dK, S^T, dP^T of tile i-1)
+        if (tid == 0 && i + 1 < nq) load_qdo(i + 1);
         __syncwarp();
         if (MODE == kBiasCode) mbar_wait(&bar_qdo[i & 1], (i >> 1) & 1);  // the code tile was written by TMA
 
@@ -397,6 +398,13 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
             const uint32_t ap = smem_u32(sPt), ad = smem_u32(sdSt);
             const uint32_t bo = smem_u32(sdO + (i & 1) * 16384), bq = smem_u32(sQ + (i & 1) * 16384), bk = smem_u32(sK);
             const uint32_t acc = i > 0 ? 1u : 0u;
+            // dQ first: it is the only product the threads wait for inside the loop (bar_dq); dV / dK accumulate under
+            // the dQ read-out and its atomics, and are covered by the next bar_sp (or bar_fin after the last tile)
+#pragma unroll
+            for (int k = 0; k < 8; ++k)  // dQ_i = dS K   (A: the dS^T tile read MN-major, k-step = 16 keys)
+                umma_bf16(tmem + cDQ, smem_desc_sw128(ad + k * 2048, 16384, 1024), smem_desc_sw128(bk + k * 2048, 8192, 1024),
+                          idesc_dq, k > 0);
+            umma_commit(&bar_dq);
 #pragma unroll
             for (int k = 0; k < 8; ++k)  // dV += P^T dO_i
                 umma_bf16(tmem + cDV, smem_desc_sw128(ap + (k >> 2) * 16384 + (k & 3) * 32, 16, 1024),
@@ -405,15 +413,12 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
             for (int k = 0; k < 8; ++k)  // dK += dS^T Q_i
                 umma_bf16(tmem + cDK, smem_desc_sw128(ad + (k >> 2) * 16384 + (k & 3) * 32, 16, 1024),
                           smem_desc_sw128(bq + k * 2048, 8192, 1024), idesc_kv, (k > 0) ? 1u : acc);
-#pragma unroll
-            for (int k = 0; k < 8; ++k)  // dQ_i = dS K   (A: the dS^T tile read MN-major, k-step = 16 keys)
-                umma_bf16(tmem + cDQ, smem_desc_sw128(ad + k * 2048, 16384, 1024), smem_desc_sw128(bk + k * 2048, 8192, 1024),
-                          idesc_dq, k > 0);
-            umma_commit(&bar_dq);
-            if (i + 1 < nq) {  // S^T / dP^T of the next tile overlap the dQ reduction below
+            if (i + 1 < nq) {  // S^T / dP^T of the next tile
                 mbar_wait(&bar_qdo[(i + 1) & 1], ((i + 1) >> 1) & 1);
                 tc_fence_after();
                 issue_s_dp(i + 1);
+            } else {
+                umma_commit(&bar_fin);
             }
         }
         __syncwarp();
@@ -433,7 +438,10 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
         tc_fence_before();  // the dQ columns are rewritten by the next tile's MMAs after the next __syncthreads
     }
 
-    // ---- epilogue: dK, dV rows of this key tile (bar_dq of the last tile covers every MMA); each half stores 32 columns
+    // ---- epilogue: dK, dV rows of this key tile; each half stores 32 columns
+    mbar_wait(&bar_fin, 0);
+    tc_fence_after();
+    __syncwarp();
     {
         float acc[32];
 #pragma unroll
