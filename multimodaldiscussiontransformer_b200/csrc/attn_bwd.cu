@@ -229,6 +229,12 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
 
         const float *nl = s_nlse[i & 1];
         const float *dl = s_delta[i & 1];
+        float nl_next = neg_inf(), dl_next = 0.f;  // lse / delta of the next query tile: the global loads fly under this tile's work
+        if (i + 1 < nq && half == 0 && (i + 1) * kTile + r < T) {
+            const size_t row = ((size_t)b * a.H + h) * T + (i + 1) * kTile + r;
+            nl_next = -a.lse[row] * kLog2e;
+            dl_next = a.delta[row];
+        }
 #pragma unroll 1
         for (int cc = half * 2; cc < half * 2 + 2; ++cc) {
             if ((!warp_keys || cc * 32 >= qvalid) && !want_gbias) {  // 32 masked keys, or 32 query columns past T: P^T = dS^T = 0
@@ -389,7 +395,10 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
                 *reinterpret_cast<uint4 *>(sdSt + off) = vd;
             }
         }
-        if (i + 1 < nq) stage_stats(i + 1);
+        if (i + 1 < nq && half == 0) {  // loaded before the softmax work of this tile, stored after it
+            s_nlse[(i + 1) & 1][r] = nl_next;
+            s_delta[(i + 1) & 1][r] = dl_next;
+        }
         fence_proxy_async();
         tc_fence_before();
         __syncthreads();
