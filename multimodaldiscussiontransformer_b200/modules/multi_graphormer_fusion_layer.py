@@ -55,12 +55,21 @@ class TextPack:
         self.text_rows = cu[seq] + nb + pos                       # packed row of every real text token
         self.padded_rows = seq * L + pos                          # its row in the padded [n * L] layout
         self.bn_rows = (cu[:-1, None] + torch.arange(nb, device=dev)[None, :]).reshape(-1)  # [n * nb]
+        # the same sequences without bottleneck slots (the trunk layers in front of the fusion stack)
+        cu0 = torch.zeros(n + 1, dtype=torch.int64, device=dev)
+        cu0[1:] = torch.cumsum(lens, 0)
+        self.text_only = _SeqLens(cu0.to(torch.int32), text_max)
 
-    def pack(self, text_padded: torch.Tensor, bottle_neck: torch.Tensor) -> torch.Tensor:
+    def gather_text(self, text_padded: torch.Tensor) -> torch.Tensor:
+        """padded ``[n, L, C]`` -> the real tokens ``[text_tokens, C]`` in sequence order (layout of ``text_only``)."""
         C = text_padded.shape[-1]
-        x = text_padded.new_empty(self.total, C)
-        x = x.index_copy(0, self.text_rows, text_padded.reshape(-1, C).index_select(0, self.padded_rows))
-        return x.index_copy(0, self.bn_rows, bottle_neck.reshape(-1, C))
+        return text_padded.reshape(-1, C).index_select(0, self.padded_rows)
+
+    def pack_tokens(self, text_tokens: torch.Tensor, bottle_neck: torch.Tensor) -> torch.Tensor:
+        """real tokens in sequence order + bottleneck -> the fusion layout."""
+        C = text_tokens.shape[-1]
+        x = text_tokens.new_empty(self.total, C)
+        return x.index_copy(0, self.text_rows, text_tokens).index_copy(0, self.bn_rows, bottle_neck.reshape(-1, C))
 
     def unpack_text(self, x: torch.Tensor) -> torch.Tensor:
         C = x.shape[-1]
@@ -68,10 +77,15 @@ class TextPack:
         return out.index_copy(0, self.padded_rows, x.index_select(0, self.text_rows)).view(self.n, self.L, C)
 
 
+class _SeqLens:
+    def __init__(self, cu_seqlens, max_seqlen):
+        self.cu_seqlens, self.max_seqlen = cu_seqlens, max_seqlen
+
+
 _FLASH = None
 
 
-def _varlen_attention(q, k, v, pack: "TextPack", dropout_p: float):
+def _varlen_attention(q, k, v, pack, dropout_p: float):
     """Self-attention over the packed sequences: ``[total, H, d]`` -> ``[total, H, d]`` (library kernel: flash-attn)."""
     global _FLASH
     if _FLASH is None:
@@ -80,7 +94,7 @@ def _varlen_attention(q, k, v, pack: "TextPack", dropout_p: float):
     return _FLASH(q, k, v, pack.cu_seqlens, pack.cu_seqlens, pack.max_seqlen, pack.max_seqlen, dropout_p=dropout_p)
 
 
-def packed_bert_layer(layer, x: torch.Tensor, pack: "TextPack") -> torch.Tensor:
+def packed_bert_layer(layer, x: torch.Tensor, pack) -> torch.Tensor:
     """Hugging Face ``BertLayer`` arithmetic (post-LN block, same parameters, same dropout rates) on packed tokens."""
     att, sa = layer.attention, layer.attention.self
     H = sa.num_attention_heads

@@ -17,7 +17,7 @@ from .. import ops
 from ._fairseq_compat import FairseqDropout, LayerNorm
 from .graphormer_graph_encoder_layer import GraphEncoderStack
 from .graphormer_layers import GraphAttnBias, GraphNodeFeature
-from .multi_graphormer_fusion_layer import GraphFusionStack, TextPack, image_rows
+from .multi_graphormer_fusion_layer import GraphFusionStack, TextPack, image_rows, packed_bert_layer
 from .multihead_attention import MultiheadAttention
 
 logger = logging.getLogger(__name__)
@@ -195,9 +195,20 @@ class MultiGraphormerGraphEncoder(nn.Module):
             ids = batched_data["x"].reshape(B * N, L).index_select(0, rows)
             type_ids = batched_data["x_token_type_ids"].reshape(B * N, L).index_select(0, rows)
             att = batched_data["x_attention_mask"].reshape(B * N, L).index_select(0, rows)
-        bert_output = self.text_model(token_type_ids=type_ids, attention_mask=att, input_ids=ids).last_hidden_state
-        n_real = bert_output.shape[0]
-        dtype = bert_output.dtype
+        n_real = ids.shape[0]
+        dtype = self.bottle_neck.weight.dtype
+        pack = None
+        if self.pack_text and batched_data.get("x_text_pack") is not None and dtype in (torch.bfloat16, torch.float16):
+            # packed (unpadded) text tokens from the embeddings on: the trunk layers in front of the fusion stack and the
+            # BERT side of every fusion layer never see a padding token
+            lens, total, longest = batched_data["x_text_pack"]
+            pack = TextPack(lens, total, longest, self.num_bottle_neck, ids.shape[1])
+            text_tokens = pack.gather_text(self.text_model.embeddings(input_ids=ids, token_type_ids=type_ids))
+            for layer in self.text_model.encoder.layer:
+                text_tokens = packed_bert_layer(layer, text_tokens, pack.text_only)
+            bert_output = None
+        else:
+            bert_output = self.text_model(token_type_ids=type_ids, attention_mask=att, input_ids=ids).last_hidden_state
         vit_output = None
         if batched_data["x_images"] is not None:
             vit_output = self.vit_model(batched_data["x_images"].to(dtype)).last_hidden_state
@@ -208,11 +219,8 @@ class MultiGraphormerGraphEncoder(nn.Module):
         bottle_neck = self.bottle_neck.weight.to(dtype).unsqueeze(0).repeat(n_real, 1, 1)                    # :339
         am = torch.cat([att.new_ones(n_real, self.num_bottle_neck), att], dim=1)
         ext_mask = ((1.0 - am[:, None, None, :].to(torch.float32)) * torch.finfo(torch.half).min).to(dtype)  # :341-354
-        pack = None
-        if self.pack_text and batched_data.get("x_text_pack") is not None and dtype in (torch.bfloat16, torch.float16):
-            lens, total, longest = batched_data["x_text_pack"]
-            pack = TextPack(lens, total, longest, self.num_bottle_neck, bert_output.shape[1])
-            x_text = pack.pack(bert_output, bottle_neck)
+        if pack is not None:
+            x_text = pack.pack_tokens(text_tokens, bottle_neck)
             x_text, vit_output, bottle_neck = self.fusion_layers[0].forward_packed(x_text, vit_output, bottle_neck, pack, img_rows)
         else:
             bert_output, vit_output, bottle_neck = self.fusion_layers[0](bert_output, vit_output, bottle_neck, ext_mask, img_rows)

@@ -198,7 +198,10 @@ def test_packed_text_fusion_matches_padded_path(name):
     assert float((a["out"] - b["out"]).abs().max()) <= 3e-2
     assert float((a["bn"] - b["bn"]).abs().max()) <= 6e-2
     assert float((a["glob"] - b["glob"]).abs().max()) <= 6e-2
-    assert float((a["text"][att] - b["text"][att]).abs().max()) <= 6e-2       # real tokens agree
+    # real tokens agree: two bf16 evaluation orders of the same layers (SDPA vs flash-attn, ATen vs fused LayerNorm);
+    # hidden states reach |x| ~ 10 where one bf16 ulp is 0.0625 => relative Frobenius 1e-2, worst element 0.13
+    assert rel(b["text"][att], a["text"][att]) <= 1e-2
+    assert float((a["text"][att] - b["text"][att]).abs().max()) <= 0.13
     assert float(b["text"][~att].abs().max()) == 0.0                            # padding positions come back as zeros
     assert abs(a["loss"] - b["loss"]) <= 2e-2 * max(1.0, abs(a["loss"]))
     for k in ("g_bn", "g_q", "g_sp"):
