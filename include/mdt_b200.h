@@ -135,9 +135,13 @@ typedef struct mdt_attn_dims {
     int64_t o_stride_b, o_stride_t, o_stride_h;
 } mdt_attn_dims;
 
+/* dropout_p in [0,1) drops attention probabilities as multihead_attention.py:196 (after the softmax, survivors scaled by
+ * 1/(1-p)); the keep mask is a counter hash of (dropout_seed, b, h, q, k) that the backward regenerates from the same
+ * seed -- nothing is stored.  dropout_p = 0 switches it off. */
 int mdt_biased_attn_fwd(const void *q, const void *k, const void *v, const mdt_attn_dims *dims,
                         const void *bias, int bias_dtype, const uint8_t *code, int code_pitch,
-                        const float *lut, const uint8_t *key_pad, void *out, float *lse, mdt_stream_t stream);
+                        const float *lut, const uint8_t *key_pad, void *out, float *lse, float dropout_p,
+                        uint64_t dropout_seed, mdt_stream_t stream);
 
 /* Diagnostics (no reference counterpart): when dev_buffer is non-null the persistent forward writes 64
  * %globaltimer stamps per CTA into it (u64 [n_ctas,64], device memory); null switches tracing off. */
@@ -147,7 +151,8 @@ int mdt_biased_attn_bwd(const void *q, const void *k, const void *v, const void 
                         const float *lse, const mdt_attn_dims *dims, const void *bias, int bias_dtype,
                         const uint8_t *code, int code_pitch, const float *lut, const uint8_t *key_pad,
                         void *dq, void *dk, void *dv, const mdt_attn_dims *grad_dims, float *dq_accum,
-                        float *delta, void *grad_bias, float *grad_lut, mdt_stream_t stream);
+                        float *delta, void *grad_bias, float *grad_lut, float dropout_p, uint64_t dropout_seed,
+                        mdt_stream_t stream);
 
 /* ------------------------------------------------------------------------------------
  * A4  GraphNodeFeature.forward               mDT/src/modules/graphormer_layers.py:39-50

@@ -41,11 +41,11 @@ SIGNATURES = {
                                   c_void_p, c_void_p]),
     "mdt_attn_bias_bwd": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "mdt_biased_attn_fwd": (c_int, [c_void_p, c_void_p, c_void_p, POINTER(AttnDims), c_void_p, c_int, c_void_p, c_int,
-                                    c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+                                    c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_uint64, c_void_p]),
     "mdt_debug_attn_trace": (c_int, [c_void_p]),
     "mdt_biased_attn_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, POINTER(AttnDims),
                                     c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
-                                    POINTER(AttnDims), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+                                    POINTER(AttnDims), c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_uint64, c_void_p]),
     "mdt_node_feature_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
                                      c_int, c_int, c_int, c_void_p, c_void_p]),
     "mdt_node_feature_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p,

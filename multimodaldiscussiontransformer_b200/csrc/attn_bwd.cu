@@ -39,6 +39,7 @@ struct BwdArgs {
     int64_t dk_sb, dk_st, dk_sh, dv_sb, dv_st, dv_sh;
     void *grad_bias;
     float *grad_lut;
+    DropArgs drop;
 };
 
 // ---------------------------------------------------------------- delta = rowsum(dO * O)
@@ -125,6 +126,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
     const int nq = (T + kTile - 1) / kTile;
     const bool want_gbias = (MODE == kBiasF32 || MODE == kBiasBF16) && a.grad_bias != nullptr;
     const bool want_glut = MODE == kBiasCode && a.grad_lut != nullptr;
+    const uint32_t salt = drop_salt(a.drop, (uint32_t)(b * a.H + h));
     const bool warp_keys = __any_sync(0xffffffffu, key_ok);  // a warp whose 32 keys are all masked only writes zeros
 
     // A key tile without a single live key has dK = dV = 0 and adds nothing to dQ or the LUT gradient.
@@ -277,8 +279,10 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
                                 x = st[e] * kLog2e;
                             }
                             const float p = ex2(x + nn[u]);
-                            const float ds = p * (dp[e] - dd[u]);
-                            st[e] = p;
+                            float keepf = 1.f;  // dropout on P: dV takes keep * P / (1 - p_drop), dS = P * (keep * dP / (1 - p_drop) - delta)
+                            if (a.drop.thr16) keepf = drop_keep_one(a.drop, salt, (uint32_t)(q0 + cc * 32 + e), (uint32_t)T, (uint32_t)key) ? a.drop.scale : 0.f;
+                            const float ds = p * (dp[e] * keepf - dd[u]);
+                            st[e] = p * keepf;
                             dp[e] = ds;
                             if (MODE == kBiasCode && want_glut) asm("ld.shared.u8 %0, [%1];" : "=r"(bin_of[e]) : "r"(bin_base + c));
                         }
@@ -355,8 +359,10 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
                     const float p = key_ok ? ex2(fmaf(st[i2 + u], kLog2e, nn[u])) : 0.f;
-                    st[i2 + u] = p;
-                    dp[i2 + u] = p * (dp[i2 + u] - dd[u]);
+                    float keepf = 1.f;
+                    if (a.drop.thr16) keepf = drop_keep_one(a.drop, salt, (uint32_t)(q0 + cc * 32 + i2 + u), (uint32_t)T, (uint32_t)key) ? a.drop.scale : 0.f;
+                    st[i2 + u] = p * keepf;
+                    dp[i2 + u] = p * (dp[i2 + u] * keepf - dd[u]);
                 }
             }
             if (want_gbias) {
@@ -510,7 +516,7 @@ extern "C" int mdt_biased_attn_bwd(const void *q, const void *k, const void *v, 
                                    const float *lse, const mdt_attn_dims *d, const void *bias, int bias_dtype,
                                    const uint8_t *code, int code_pitch, const float *lut, const uint8_t *key_pad, void *dq,
                                    void *dk, void *dv, const mdt_attn_dims *g, float *dq_accum, float *delta,
-                                   void *grad_bias, float *grad_lut, mdt_stream_t stream) {
+                                   void *grad_bias, float *grad_lut, float dropout_p, uint64_t dropout_seed, mdt_stream_t stream) {
     if (int rc = require_sm100()) return rc;
     if (int rc = check_dims(d, "mdt_biased_attn_bwd")) return rc;
     if (int rc = check_dims(g, "mdt_biased_attn_bwd(grad_dims)")) return rc;
@@ -521,6 +527,7 @@ extern "C" int mdt_biased_attn_bwd(const void *q, const void *k, const void *v, 
     MDT_REQUIRE(bias == nullptr || bias_dtype == MDT_F32 || bias_dtype == MDT_BF16, "mdt_biased_attn_bwd: bad bias dtype");
     MDT_REQUIRE(grad_bias == nullptr || bias != nullptr, "mdt_biased_attn_bwd: grad_bias needs bias");
     MDT_REQUIRE(grad_lut == nullptr || code != nullptr, "mdt_biased_attn_bwd: grad_lut needs code");
+    MDT_REQUIRE(dropout_p >= 0.f && dropout_p < 1.f, "mdt_biased_attn_bwd: dropout_p must be in [0, 1)");
     if (code) {
         MDT_REQUIRE(lut != nullptr, "mdt_biased_attn_bwd: code needs lut");
         MDT_REQUIRE(code_pitch >= d->T, "mdt_biased_attn_bwd: code_pitch must be >= T");
@@ -555,6 +562,7 @@ extern "C" int mdt_biased_attn_bwd(const void *q, const void *k, const void *v, 
     a.dk_sb = g->k_stride_b, a.dk_st = g->k_stride_t, a.dk_sh = g->k_stride_h;
     a.dv_sb = g->v_stride_b, a.dv_st = g->v_stride_t, a.dv_sh = g->v_stride_h;
     a.grad_bias = grad_bias, a.grad_lut = grad_lut;
+    a.drop = make_drop(dropout_p, dropout_seed);
     const int mode = bias_mode(bias, bias_dtype, code);
     a.Tmain = tail_split(T, mode == kBiasCode || mode == kBiasNone);
     CUtensorMap mc = mq;  // only read by the code mode
@@ -583,6 +591,7 @@ extern "C" int mdt_biased_attn_bwd(const void *q, const void *k, const void *v, 
         t.delta = delta, t.dq_accum = dq_accum, t.dk = a.dk, t.dv = a.dv;
         t.dk_sb = a.dk_sb, t.dk_st = a.dk_st, t.dk_sh = a.dk_sh, t.dv_sb = a.dv_sb, t.dv_st = a.dv_st, t.dv_sh = a.dv_sh;
         t.grad_lut = grad_lut;
+        t.drop = a.drop;
         if (int rc3 = launch_bwd_tails(t, st)) return rc3;
     }
     {

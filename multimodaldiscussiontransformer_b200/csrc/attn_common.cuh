@@ -26,6 +26,45 @@ inline int bias_mode(const void *bias, int bias_dtype, const uint8_t *code) {
     return bias_dtype == MDT_F32 ? kBiasF32 : kBiasBF16;
 }
 
+// ---- attention dropout (multihead_attention.py:196): the keep mask is a counter hash, never stored.
+//   salt(b,h) = fmix32(seed_lo ^ (b*H+h) * 0x9e3779b1) + seed_hi
+//   hp(q,k)   = mix(salt ^ (q*T + (k & ~1)));   r16 = k odd ? hp & 0xffff : hp >> 16;   keep <=> r16 >= thr16
+// so the forward (a thread walks along k: one hash per two elements) and the backward (a thread owns one key: one
+// hash per element) regenerate the same mask from (seed, b, h, q, k).  thr16 == 0 switches dropout off.
+struct DropArgs {
+    uint32_t thr16;   // round(p * 65536)
+    float scale;      // 1 / (1 - p)
+    uint32_t seed_lo, seed_hi;
+};
+inline DropArgs make_drop(float p, uint64_t seed) {
+    DropArgs d;
+    const float t = p * 65536.f + 0.5f;
+    d.thr16 = p <= 0.f ? 0u : (t >= 65535.f ? 65535u : (uint32_t)t);
+    d.scale = 1.f / (1.f - p);
+    d.seed_lo = (uint32_t)seed, d.seed_hi = (uint32_t)(seed >> 32);
+    return d;
+}
+__device__ __forceinline__ uint32_t drop_salt(const DropArgs &d, uint32_t bh) {
+    uint32_t h = d.seed_lo ^ (bh * 0x9e3779b1u);
+    h ^= h >> 16;
+    h *= 0x85ebca6bu;
+    h ^= h >> 13;
+    h *= 0xc2b2ae35u;
+    h ^= h >> 16;
+    return h + d.seed_hi;
+}
+__device__ __forceinline__ uint32_t drop_hash(uint32_t salt, uint32_t e_even) {  // e_even = q*T + (k & ~1)
+    uint32_t x = (salt ^ e_even) * 0x9e3779b1u;
+    x ^= x >> 15;
+    x *= 0x85ebca77u;
+    x ^= x >> 13;
+    return x;
+}
+__device__ __forceinline__ bool drop_keep_one(const DropArgs &d, uint32_t salt, uint32_t q, uint32_t T, uint32_t k) {
+    const uint32_t hp = drop_hash(salt, q * T + (k & ~1u));
+    return ((k & 1u) ? (hp & 0xffffu) : (hp >> 16)) >= d.thr16;
+}
+
 // TMA view of a strided bf16 tensor addressed (b, t, h, c): dims innermost-first {64, T, H, B},
 // box {64, rows, 1, 1}, 128-byte swizzle.  Rows past T read as zeros.
 inline int make_bthd_map(CUtensorMap *map, const void *base, int B, int H, int T, int64_t sb, int64_t st, int64_t sh,
@@ -55,6 +94,7 @@ struct Fwd2Args {
     __nv_bfloat16 *out;
     int64_t o_sb, o_st, o_sh;
     float *lse;
+    DropArgs drop;
     int Tmain;                  // queries / keys processed: [0, Tmain) (= T; kept separate from the row pitch T)
     unsigned long long *trace;  // diagnostics: per-CTA globaltimer stamps (mdt_debug_attn_trace), else null
 };
@@ -85,6 +125,7 @@ struct TailArgs {
     __nv_bfloat16 *dk, *dv;
     int64_t dk_sb, dk_st, dk_sh, dv_sb, dv_st, dv_sh;
     float *grad_lut;
+    DropArgs drop;
 };
 int launch_bwd_tails(const TailArgs &a, cudaStream_t st);
 

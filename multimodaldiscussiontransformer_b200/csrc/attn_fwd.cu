@@ -25,6 +25,7 @@ struct FwdArgs {
     __nv_bfloat16 *out;
     int64_t o_sb, o_st, o_sh;
     float *lse;
+    DropArgs drop;
 };
 
 constexpr int kFwdSmem = 16384 /*Q*/ + 3 * 16384 /*K/V ring*/ + 32768 /*P*/ + 1024 /*alignment slack*/;
@@ -199,6 +200,15 @@ __global__ void __launch_bounds__(128, 2)
             sum += s[i];
         }
         l += sum;
+        if (a.drop.thr16) {  // dropout on P (multihead_attention.py:196); the row sum above is of the undropped p
+            const uint32_t salt = drop_salt(a.drop, (uint32_t)(b * a.H + h)), row = (uint32_t)q * (uint32_t)T;
+#pragma unroll
+            for (int i = 0; i < 128; i += 2) {
+                const uint32_t hp = drop_hash(salt, row + (uint32_t)(k0 + i));
+                s[i] = (hp >> 16) >= a.drop.thr16 ? s[i] * a.drop.scale : 0.f;
+                s[i + 1] = (hp & 0xffffu) >= a.drop.thr16 ? s[i + 1] * a.drop.scale : 0.f;
+            }
+        }
         // ---- P (bf16) -> swizzled K-major A tile: two 64-key halves of 16 KB
 #pragma unroll
         for (int ch = 0; ch < 16; ++ch) {
@@ -287,7 +297,8 @@ extern "C" int mdt_debug_attn_trace(unsigned long long *dev_buffer) {
 
 extern "C" int mdt_biased_attn_fwd(const void *q, const void *k, const void *v, const mdt_attn_dims *d, const void *bias,
                                    int bias_dtype, const uint8_t *code, int code_pitch, const float *lut,
-                                   const uint8_t *key_pad, void *out, float *lse, mdt_stream_t stream) {
+                                   const uint8_t *key_pad, void *out, float *lse, float dropout_p, uint64_t dropout_seed,
+                                   mdt_stream_t stream) {
     if (int rc = require_sm100()) return rc;
     if (int rc = check_dims(d, "mdt_biased_attn_fwd")) return rc;
     MDT_REQUIRE(q && k && v && out, "mdt_biased_attn_fwd: q, k, v, out must be non-null");
@@ -295,6 +306,7 @@ extern "C" int mdt_biased_attn_fwd(const void *q, const void *k, const void *v, 
                 "mdt_biased_attn_fwd: out must be 16-byte aligned with strides that are multiples of 8");
     MDT_REQUIRE(!(bias && code), "mdt_biased_attn_fwd: pass a materialised bias or a code/lut pair, not both");
     MDT_REQUIRE(bias == nullptr || bias_dtype == MDT_F32 || bias_dtype == MDT_BF16, "mdt_biased_attn_fwd: bad bias dtype");
+    MDT_REQUIRE(dropout_p >= 0.f && dropout_p < 1.f, "mdt_biased_attn_fwd: dropout_p must be in [0, 1)");
     if (code) {
         MDT_REQUIRE(lut != nullptr, "mdt_biased_attn_fwd: code needs lut");
         MDT_REQUIRE(code_pitch >= d->T && code_pitch % 16 == 0 && ((uintptr_t)code & 15) == 0,
@@ -310,6 +322,7 @@ extern "C" int mdt_biased_attn_fwd(const void *q, const void *k, const void *v, 
     a.out = reinterpret_cast<__nv_bfloat16 *>(out);
     a.o_sb = d->o_stride_b, a.o_st = d->o_stride_t, a.o_sh = d->o_stride_h;
     a.lse = lse;
+    a.drop = make_drop(dropout_p, dropout_seed);
     cudaStream_t st = as_stream(stream);
     const int mode = bias_mode(bias, bias_dtype, code);
     if ((mode == kBiasNone || mode == kBiasCode) && d->T > kTile && d->T <= kFwd3MaxT) {  // persistent warp-specialised kernel (attn_fwd3.cu)
@@ -321,6 +334,7 @@ extern "C" int mdt_biased_attn_fwd(const void *q, const void *k, const void *v, 
         a2.B = d->B, a2.H = d->H, a2.T = d->T, a2.has_code = code != nullptr, a2.lut = lut, a2.key_pad = key_pad;
         a2.out = a.out, a2.o_sb = a.o_sb, a2.o_st = a.o_st, a2.o_sh = a.o_sh, a2.lse = lse;
         a2.trace = g_attn_trace;
+        a2.drop = a.drop;
         a2.Tmain = d->T;
         return launch_fwd3(mq, mk, mv, mc, a2, st);
     }

@@ -303,6 +303,7 @@ __global__ void __launch_bounds__(kF3Threads, 1)
             if (tid == 0) f3_trace(a, 2 + 12 * n + 0);
             const uint32_t lut_base = smem_u32(ctl.lut[buf]);
             float m_used = neg_inf(), l = 0.f;   // m_used in log2 units (scores are scaled by log2 e on the fly)
+            const uint32_t salt = drop_salt(a.drop, (uint32_t)(it.b * H + it.h)), drop_row = (uint32_t)q * (uint32_t)T;
 
             for (int j = 0; j < nkv; ++j, ++g) {
                 const int s = g & 1;
@@ -423,7 +424,12 @@ __global__ void __launch_bounds__(kF3Threads, 1)
                                     fadd2(x[i], x[i + 1], x[i], x[i + 1], nm, nm);
                                     x[i] = ex2(x[i]);
                                     x[i + 1] = ex2(x[i + 1]);
-                                    fadd2(sum0, sum1, sum0, sum1, x[i], x[i + 1]);
+                                    fadd2(sum0, sum1, sum0, sum1, x[i], x[i + 1]);   // the row sum is of the undropped p
+                                    if (a.drop.thr16) {  // dropout on P (multihead_attention.py:196): keys k, k + 1 share one hash
+                                        const uint32_t hp = drop_hash(salt, drop_row + (uint32_t)(j * kTile + hf * 64 + ch * 8 + i));
+                                        x[i] = (hp >> 16) >= a.drop.thr16 ? x[i] * a.drop.scale : 0.f;
+                                        x[i + 1] = (hp & 0xffffu) >= a.drop.thr16 ? x[i + 1] * a.drop.scale : 0.f;
+                                    }
                                 }
                                 uint4 v;
                                 v.x = pack_bf16x2(x[0], x[1]);

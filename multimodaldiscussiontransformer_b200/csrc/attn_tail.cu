@@ -71,6 +71,7 @@ __global__ void __launch_bounds__(kTailThreads, 1) attn_bwd_tail_k_kernel(const 
     const int h = blockIdx.x, b = blockIdx.y, T = a.T;
     const bool want_glut = HAS_CODE && a.grad_lut != nullptr;
     tail_stage_lut<HAS_CODE>(s_lut, a, h);
+    const uint32_t salt = drop_salt(a.drop, (uint32_t)(b * a.H + h));
     float mybin = 0.f;
     for (int k = a.Tmain; k < T; ++k) {
         __nv_bfloat16 *dkp = a.dk + (size_t)b * a.dk_sb + (size_t)k * a.dk_st + (size_t)h * a.dk_sh;
@@ -108,9 +109,12 @@ __global__ void __launch_bounds__(kTailThreads, 1) attn_bwd_tail_k_kernel(const 
                     code = a.code[((size_t)b * T + q) * a.code_pitch + k];
                     x += s_lut[code];
                 }
-                const float p = sm100::ex2(x);
-                ds = p * (dp - a.delta[row]);
-                if (p != 0.f) {
+                const float p0 = sm100::ex2(x);
+                float keepf = 1.f;
+                if (a.drop.thr16) keepf = drop_keep_one(a.drop, salt, (uint32_t)q, (uint32_t)T, (uint32_t)k) ? a.drop.scale : 0.f;
+                ds = p0 * (dp * keepf - a.delta[row]);
+                const float p = p0 * keepf;  // what dV sees
+                if (p0 != 0.f) {
                     float4 *dq = reinterpret_cast<float4 *>(a.dq_accum + row * 64);
 #pragma unroll
                     for (int c = 0; c < 64; c += 4) {

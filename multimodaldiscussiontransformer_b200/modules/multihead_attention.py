@@ -88,8 +88,6 @@ class MultiheadAttention(nn.Module):
             raise NotImplementedError(
                 "the B200 attention kernel never materialises the [B*H,T,T] weights; the mDT hot path calls "
                 "MultiheadAttention with need_weights=False (graphormer_graph_encoder_layer.py:124)")
-        if self.training and self.dropout_module.p > 0:
-            raise NotImplementedError("attention dropout inside the fused kernel is not available yet; use attention_dropout=0")
         if key_padding_mask is not None and key_padding_mask.dim() == 0:
             key_padding_mask = None
         if key_padding_mask is not None:
@@ -109,7 +107,9 @@ class MultiheadAttention(nn.Module):
         if attn_mask is not None:  # additive [T,T] mask (multihead_attention.py:176-178)
             m = attn_mask.to(torch.float32).view(1, 1, tgt_len, tgt_len)
             bias = m.expand(bsz, self.num_heads, tgt_len, tgt_len) if bias is None else bias.float() + m
-        o = ops.biased_attention(q, k, v, bias=bias, code=code, lut=lut, key_padding_mask=key_padding_mask)
+        # attention dropout (multihead_attention.py:196) happens inside the kernel: counter-hash mask, regenerated in the backward
+        p_drop = float(self.dropout_module.p) if self.training else 0.0
+        o = ops.biased_attention(q, k, v, bias=bias, code=code, lut=lut, key_padding_mask=key_padding_mask, dropout_p=p_drop)
         # o: [B,T,H,64] stored t-major, i.e. [T,B,H,64] in memory
         o = o.permute(1, 0, 2, 3)
         if self.head_dim != KERNEL_HEAD_DIM:

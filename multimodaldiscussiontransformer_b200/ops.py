@@ -229,7 +229,7 @@ def _empty_like_layout(q: torch.Tensor) -> torch.Tensor:
 
 class _BiasedAttention(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, q, k, v, bias, code, lut, key_pad):
+    def forward(ctx, q, k, v, bias, code, lut, key_pad, dropout_p, seed):
         _require_cuda(q, k, v, bias, code, lut, key_pad)
         lib = _lib.load()
         q, k, v = _check_bthd("q", q), _check_bthd("k", k), _check_bthd("v", v)
@@ -256,9 +256,11 @@ class _BiasedAttention(torch.autograd.Function):
             _lib.check(lib.mdt_biased_attn_fwd(_lib.ptr(q), _lib.ptr(k), _lib.ptr(v), ctypes.byref(dims), _lib.ptr(bias),
                                                _lib.dtype_code(bias.dtype) if bias is not None else 0, _lib.ptr(code),
                                                pitch, _lib.ptr(lut) if code is not None else None, _lib.ptr(key_pad),
-                                               _lib.ptr(out), _lib.ptr(lse), _lib.stream()), "mdt_biased_attn_fwd")
+                                               _lib.ptr(out), _lib.ptr(lse), float(dropout_p), int(seed), _lib.stream()),
+                       "mdt_biased_attn_fwd")
         ctx.save_for_backward(q, k, v, out, lse, bias, code, lut if code is not None else None, key_pad)
         ctx.pitch = pitch
+        ctx.drop = (float(dropout_p), int(seed))
         return out
 
     @staticmethod
@@ -281,26 +283,33 @@ class _BiasedAttention(torch.autograd.Function):
                 _lib.ptr(q), _lib.ptr(k), _lib.ptr(v), _lib.ptr(out), _lib.ptr(go), _lib.ptr(lse), ctypes.byref(dims),
                 _lib.ptr(bias), _lib.dtype_code(bias.dtype) if bias is not None else 0, _lib.ptr(code), ctx.pitch,
                 _lib.ptr(lut), _lib.ptr(key_pad), _lib.ptr(dq), _lib.ptr(dk), _lib.ptr(dv), ctypes.byref(gdims),
-                _lib.ptr(dq_accum), _lib.ptr(delta), _lib.ptr(g_bias), _lib.ptr(g_lut), _lib.stream()),
-                "mdt_biased_attn_bwd")
-        return dq, dk, dv, g_bias, None, g_lut, None
+                _lib.ptr(dq_accum), _lib.ptr(delta), _lib.ptr(g_bias), _lib.ptr(g_lut), ctx.drop[0], ctx.drop[1],
+                _lib.stream()), "mdt_biased_attn_bwd")
+        return dq, dk, dv, g_bias, None, g_lut, None, None, None
 
 
 def biased_attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, bias: Optional[torch.Tensor] = None,
                      code: Optional[torch.Tensor] = None, lut: Optional[torch.Tensor] = None,
-                     key_padding_mask: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """``softmax_fp32(q k^T + bias [+ key padding -> -inf]) v`` on the tcgen05 kernel.
+                     key_padding_mask: Optional[torch.Tensor] = None, dropout_p: float = 0.0,
+                     seed: Optional[int] = None) -> torch.Tensor:
+    """``dropout(softmax_fp32(q k^T + bias [+ key padding -> -inf])) v`` on the tcgen05 kernel.
 
     ``q, k, v``: bf16 ``[B, T, H, 64]`` (any strides that are multiples of 8; ``q`` already scaled by
     ``d^-0.5`` as at multihead_attention.py:137).  ``bias``: materialised ``[B,H,T,T]`` (f32 | bf16) **or**
     ``code`` uint8 ``[B,T,pitch]`` with ``lut`` f32 ``[H,256]`` (bias = ``lut[h, code]``, code 255 = -inf).
+    ``dropout_p`` drops attention probabilities (multihead_attention.py:196) with a counter-hash mask seeded by ``seed``
+    (default: drawn from torch's CPU generator, so ``torch.manual_seed`` reproduces it); the backward regenerates it.
     Returns ``[B, T, H, 64]`` bf16 laid out like ``q``.
     """
     if bias is not None and code is not None:
         raise ValueError("pass either a materialised bias or code+lut")
     if code is not None and lut is None:
         raise ValueError("code needs lut")
-    return _BiasedAttention.apply(q, k, v, bias, code, lut, key_padding_mask)
+    if not 0.0 <= dropout_p < 1.0:
+        raise ValueError("dropout_p must be in [0, 1)")
+    if seed is None:
+        seed = int(torch.randint(0, 2 ** 62, (1,)).item()) if dropout_p > 0.0 else 0
+    return _BiasedAttention.apply(q, k, v, bias, code, lut, key_padding_mask, float(dropout_p), int(seed))
 
 
 # ------------------------------------------------------------------------------------------

@@ -254,3 +254,84 @@ def test_backward_T1025(ops):
     got, want = run_backward(ops, q, k, v, code=code, lut=lut)
     for name in want:
         assert rel_err(got[name], want[name]) <= GRAD_RTOL, name
+
+
+# ---------------------------------------------------------------------------------------------
+# attention dropout (multihead_attention.py:196): the kernels' counter-hash mask, restated in torch
+# ---------------------------------------------------------------------------------------------
+_M32 = 0xFFFFFFFF
+
+
+def dropout_keep_mask(seed, p, B, H, T, device="cuda"):
+    """bool [B,H,T,T]: csrc/attn_common.cuh drop_salt / drop_hash / drop_keep_one in 64-bit integer torch ops."""
+    thr = min(65535, int(p * 65536.0 + 0.5))
+    lo, hi = seed & _M32, (seed >> 32) & _M32
+    bh = torch.arange(B * H, dtype=torch.int64, device=device)
+    h = (lo ^ ((bh * 0x9E3779B1) & _M32)) & _M32
+    h = h ^ (h >> 16)
+    h = (h * 0x85EBCA6B) & _M32
+    h = h ^ (h >> 13)
+    h = (h * 0xC2B2AE35) & _M32
+    h = h ^ (h >> 16)
+    salt = ((h + hi) & _M32).view(B * H, 1, 1)
+    q = torch.arange(T, dtype=torch.int64, device=device).view(1, T, 1)
+    k = torch.arange(T, dtype=torch.int64, device=device).view(1, 1, T)
+    e = (q * T + (k & ~1)) & _M32
+    x = ((salt ^ e) * 0x9E3779B1) & _M32
+    x = x ^ (x >> 15)
+    x = (x * 0x85EBCA77) & _M32
+    x = x ^ (x >> 13)
+    r16 = torch.where((k & 1) == 1, x & 0xFFFF, x >> 16)
+    return (r16 >= thr).view(B, H, T, T)
+
+
+def reference_dropout(q, k, v, bias, key_pad, keep, p):
+    s = torch.einsum("bthd,bshd->bhts", q.float(), k.float())
+    if bias is not None:
+        s = s + bias.float()
+    if key_pad is not None:
+        s = s.masked_fill(key_pad[:, None, None, :].bool(), NEG)
+    pr = torch.softmax(s, dim=-1) * keep.float() / (1.0 - p)
+    return torch.einsum("bhts,bshd->bthd", pr, v.float())
+
+
+@pytest.mark.parametrize("T", [64, 129, 200, 385])
+@pytest.mark.parametrize("mode", ["none", "bf16", "code"])
+def test_attention_dropout_forward_backward(ops, T, mode):
+    """Forward and gradients with dropout_p = 0.3 against the fp32 formula using the very same mask; T = 64 runs the
+    single-tile kernel, 129 / 385 the persistent forward plus the tail-key backward kernel, 200 a ragged last tile."""
+    B, H, p, seed = 2, 4, 0.3, 0x1234_5678_9ABC
+    q, k, v = make_qkv(B, T, H, seed=11 + T)
+    kp = key_padding(B, T, T) if T != 129 else None
+    bias = code = lut = None
+    if mode == "bf16":
+        bias = make_bias(B, H, T, T).bfloat16().requires_grad_(True)
+        ref_bias = bias.detach().float().requires_grad_(True)
+    elif mode == "code":
+        code, lut = make_code(B, H, T, T)
+        lut.requires_grad_(True)
+        lut_r = lut.detach().clone().requires_grad_(True)
+        c = code[:, :, :T].long()
+        ref_bias = lut_r[:, c.reshape(-1)].reshape(H, B, T, T).permute(1, 0, 2, 3).masked_fill((c == 255).unsqueeze(1), NEG)
+    else:
+        ref_bias = None
+    keep = dropout_keep_mask(seed, p, B, H, T)
+    assert abs(float(keep.float().mean()) - (1 - p)) < 2e-2
+    qs, ks, vs = (t.detach().requires_grad_(True) for t in (q, k, v))
+    o = ops.biased_attention(qs, ks, vs, bias=bias, code=code, lut=lut, key_padding_mask=kp, dropout_p=p, seed=seed)
+    qr, kr, vr = (t.detach().float().requires_grad_(True) for t in (q, k, v))
+    o_ref = reference_dropout(qr, kr, vr, ref_bias, kp, keep, p)
+    assert float((o.float() - o_ref).abs().max()) <= 3e-2
+    go = torch.randn(B, T, H, 64, generator=torch.Generator().manual_seed(5)).cuda()
+    ins = [qs, ks, vs] + ([bias] if mode == "bf16" else []) + ([lut] if mode == "code" else [])
+    ins_r = [qr, kr, vr] + ([ref_bias] if mode == "bf16" else []) + ([lut_r] if mode == "code" else [])
+    got = torch.autograd.grad(o, ins, go.bfloat16())
+    want = torch.autograd.grad(o_ref, ins_r, go.bfloat16().float())
+    for name, a, b_ in zip(("dq", "dk", "dv", "dbias/dlut"), got, want):
+        num, den = float((a.float() - b_).norm()), float(b_.norm())
+        assert num <= GRAD_RTOL * max(den, 1e-6), (name, num / max(den, 1e-6))
+    # dropout_p = 0 through the same entry leaves the deterministic result
+    o0 = ops.biased_attention(q, k, v, bias=None if bias is None else bias.detach(), code=code,
+                              lut=None if lut is None else lut.detach(), key_padding_mask=kp)
+    o0_ref = reference(q, k, v, None if ref_bias is None else ref_bias.detach(), kp)
+    assert float((o0.float() - o0_ref).abs().max()) <= FWD_ATOL
