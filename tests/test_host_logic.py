@@ -125,3 +125,38 @@ def test_criterion_matches_oracle_loss():
     assert n == n2 == 3 and abs(float(loss) - float(want)) < 1e-6
     agg = crit.aggregate([log])
     assert 0.0 <= agg["accuracy"] <= 1.0 and "f1" in agg
+
+
+def test_text_pack_round_trip_and_host_lengths():
+    """the packed (unpadded) token layout of the fusion layers -- index construction is plain torch, so it
+    is checked here on CPU: every real token and bottleneck slot lands in exactly one packed row and comes back."""
+    from multimodaldiscussiontransformer_b200.data import synthetic as syn
+    from multimodaldiscussiontransformer_b200.data.collator import HostBatch
+    from multimodaldiscussiontransformer_b200.modules.multi_graphormer_fusion_layer import TextPack
+
+    items = syn.synthetic_items([5, 9, 3], 11, with_images=False, as_torch=False)
+    hb = HostBatch(items, pin=False)
+    att = hb.tensors["text"][2] != 0                                  # [n_real, L]
+    lens = att.sum(1).to(torch.int32)
+    assert hb.text_prefix and hb.text_tokens == int(lens.sum()) and hb.text_max == int(lens.max())
+    assert torch.equal(hb.tensors["ints"][-hb.n_real:], lens)         # lengths ride at the end of the int32 staging buffer
+    n, L, nb, C = hb.n_real, hb.L, 4, 8
+    pack = TextPack(lens, hb.text_tokens, hb.text_max, nb, L)
+    assert pack.total == hb.text_tokens + nb * n and pack.max_seqlen == hb.text_max + nb
+    assert torch.equal(pack.cu_seqlens[1:] - pack.cu_seqlens[:-1], lens + nb)
+    assert torch.equal(pack.text_only.cu_seqlens[1:] - pack.text_only.cu_seqlens[:-1], lens)
+    rows = torch.cat([pack.text_rows, pack.bn_rows])
+    assert rows.numel() == pack.total and torch.equal(rows.sort().values, torch.arange(pack.total))
+    g = torch.Generator().manual_seed(0)
+    text = torch.randn(n, L, C, generator=g) * att[:, :, None]
+    bn = torch.randn(n, nb, C, generator=g)
+    x = pack.pack_tokens(pack.gather_text(text), bn)
+    assert torch.equal(pack.unpack_text(x), text)                     # padding positions come back as zeros
+    assert torch.equal(x.index_select(0, pack.bn_rows).view(n, nb, C), bn)
+    # sequence i occupies [cu[i], cu[i+1]): bottleneck slots first, then its tokens in order
+    i = 1
+    lo = int(pack.cu_seqlens[i])
+    assert torch.equal(x[lo:lo + nb], bn[i]) and torch.equal(x[lo + nb:lo + nb + int(lens[i])], text[i, :int(lens[i])])
+    # a mask with a hole is not a prefix: the collator then does not offer the packed path
+    items[0].x["attention_mask"][0, 1] = 0
+    assert not HostBatch(items, pin=False).text_prefix
