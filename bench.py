@@ -168,6 +168,23 @@ def run_reference(args):
     print(json.dumps(line))
 
 
+def instep_traffic():
+    """DRAM bytes (read + write) of the attention kernels of one forward + one backward call inside a cfg3 training step,
+    from the committed `ncu --set full` capture of bench.py (profiles/attn_instep_traffic_r01.json, tools/ncu_traffic.py);
+    None when the capture is absent."""
+    path = os.path.join(ROOT, "profiles", "attn_instep_traffic_r01.json")
+    if not os.path.isfile(path):
+        return None
+    try:
+        ks = json.load(open(path))["kernels"]
+        per_name = {}
+        for k in ks:  # one launch of each kernel kind
+            per_name.setdefault(k["name"], k["dram_bytes"])
+        return float(sum(per_name.values()))
+    except Exception:
+        return None
+
+
 # ---------------------------------------------------------------------------------------------
 # B200 arm
 # ---------------------------------------------------------------------------------------------
@@ -283,7 +300,7 @@ def run_b200(args):
     achieved = (flop_fwd + flop_bwd) / ((fwd_ms + bwd_ms) * 1e-3) / 1e12
     roofline = {"bound": "tensor", "kernel": "attn_fwd_kernel + attn_bwd_kernel (biased attention, code+lut bias)",
                 "achieved": achieved, "peak": peaks["tf_sustained"], "unit": "TFLOP/s", "frac": achieved / peaks["tf_sustained"],
-                "traffic": None, "peak_source": peaks["source"] + ", sustained bf16", "fwd_us": fwd_ms * 1e3, "bwd_us": bwd_ms * 1e3,
+                "traffic": instep_traffic(), "peak_source": peaks["source"] + ", sustained bf16", "fwd_us": fwd_ms * 1e3, "bwd_us": bwd_ms * 1e3,
                 "fwd_tflops": flop_fwd / (fwd_ms * 1e-3) / 1e12, "bwd_tflops": flop_bwd / (bwd_ms * 1e-3) / 1e12,
                 "launches_timed": len(fwd) + len(bwd), "attn_share_of_step": (sum(fwd) + sum(bwd)) / ms_total}
 

@@ -38,7 +38,7 @@ for n, v in step:
     a[0] += 1
     a[1] += v
 mine = ("mdt::", "attn_fwd_kernel", "attn_bwd_kernel", "apsp", "edges_to_adj", "node_feature", "move_rows", "attn_bias",
-        "attn_delta", "attn_dq", "mdt_")
+        "attn_delta", "attn_dq", "mdt_", "attn::", "ln::")
 print(f"{'kernel':72s} {'count':>6s} {'total us':>11s} {'share':>7s} {'avg us':>9s}")
 for k, (c, t) in sorted(agg.items(), key=lambda kv: -kv[1][1])[:28]:
     print(f"{k:72s} {c:6d} {t:11.1f} {100 * t / tot:6.2f}% {t / c:9.1f}")
