@@ -185,6 +185,35 @@ def instep_traffic():
         return None
 
 
+def attention_cfg4(peaks, T=1025, iters=10):
+    """The attention kernels alone at SURVEY 8d's cfg4 size (B=32, H=12, T=1025, code + LUT bias, 25 % key padding), timed
+    live after the training steps with the same events around the C-ABI call: the cfg3 step only has T=129, where two
+    128-wide tiles hold 129 tokens and the kernels are latency-bound."""
+    import torch
+    sys.path.insert(0, os.path.join(ROOT, "benchmarks"))
+    import attn_microbench as mb
+    from multimodaldiscussiontransformer_b200 import ops
+    B, H = 32, 12
+    q, k, v, kw = mb.make_inputs(B, H, T, "code")
+    o = ops.biased_attention(q, k, v, **kw)
+    go = torch.randn_like(o)
+    inputs = [q, k, v, kw["lut"]]
+
+    def fwd():
+        with torch.no_grad():
+            ops.biased_attention(q, k, v, **kw)
+
+    def bwd():
+        torch.autograd.grad(o, inputs, go, retain_graph=True)
+
+    f_ms, b_ms = mb.time_it(fwd, iters, None, "fwd"), mb.time_it(bwd, iters, None, "bwd")
+    ff, fb = 4.0 * B * H * T * T * 64, 8.0 * B * H * T * T * 64
+    ach = (ff + fb) / ((f_ms + b_ms) * 1e-3) / 1e12
+    return {"B": B, "H": H, "T": T, "fwd_us": f_ms * 1e3, "bwd_us": b_ms * 1e3, "fwd_tflops": ff / f_ms / 1e9, "bwd_tflops": fb / b_ms / 1e9,
+            "achieved": ach, "peak": peaks["tf_burst"], "frac": ach / peaks["tf_burst"], "unit": "TFLOP/s",
+            "peak_kind": "burst bf16 (kernels timed alone)", "iters": iters}
+
+
 # ---------------------------------------------------------------------------------------------
 # B200 arm
 # ---------------------------------------------------------------------------------------------
@@ -304,10 +333,27 @@ def run_b200(args):
                 "fwd_tflops": flop_fwd / (fwd_ms * 1e-3) / 1e12, "bwd_tflops": flop_bwd / (bwd_ms * 1e-3) / 1e12,
                 "launches_timed": len(fwd) + len(bwd), "attn_share_of_step": (sum(fwd) + sum(bwd)) / ms_total}
 
+    # the LayerNorm kernels (HBM-bound) are the largest share of the step among this library's kernels
+    ln_b = ln_ms = 0.0
+    for k, s_, e_, rows_, C_, flags in events:
+        if k == "ln_fwd":
+            ln_b += rows_ * C_ * 2.0 * (2 + (flags >> 1) + (flags & 1)) + rows_ * 8.0   # x, y (+ residual) (+ z) + mean / rstd
+        elif k == "ln_bwd":
+            ln_b += rows_ * C_ * 2.0 * (2 + flags) + rows_ * 8.0                         # dy, z, gradients written
+        else:
+            continue
+        ln_ms += s_.elapsed_time(e_)
+    if ln_ms > 0:
+        roofline["layernorm"] = {"bound": "hbm", "kernel": "ln_fwd_kernel + ln_bwd_kernel (dropout + residual + LayerNorm)",
+                                 "achieved": ln_b / (ln_ms * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                                 "frac": ln_b / (ln_ms * 1e-3) / 1e9 / peaks["hbm_gbs"], "share_of_step": ln_ms / ms_total}
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
+    if world == 1:
+        roofline["attn_T1025"] = attention_cfg4(peaks)
     cpu = None
     if not args.no_cpu_baseline and world == 1:
         cpu, _ = cpu_reference_arm(n, 2, 1, args.image_frac, DROPOUTS)

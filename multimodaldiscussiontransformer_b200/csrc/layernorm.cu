@@ -56,6 +56,12 @@ __device__ __forceinline__ uint4 pack8(const float *f) {
     for (int i = 0; i < 4; ++i) p[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
     return v;
 }
+// streaming 16-byte load (read once: keep it out of L1)
+__device__ __forceinline__ uint4 ldg_stream(const uint4 *p) {
+    uint4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    return v;
+}
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -84,13 +90,26 @@ __global__ void __launch_bounds__(kThreads) ln_fwd_kernel(const FwdArgs a) {
         unpack8(reinterpret_cast<const uint4 *>(a.gamma)[v * 32 + lane], g[v]);
         unpack8(reinterpret_cast<const uint4 *>(a.beta)[v * 32 + lane], bta[v]);
     }
+    // the raw vectors of the next row are requested before this row is reduced: two rows of loads in flight per warp
+    uint4 nx[VEC], nr[VEC];
+    auto fetch = [&](int64_t row) {
+#pragma unroll
+        for (int v = 0; v < VEC; ++v) {
+            nx[v] = ldg_stream(reinterpret_cast<const uint4 *>(a.x + row * C) + v * 32 + lane);
+            if (a.res) nr[v] = ldg_stream(reinterpret_cast<const uint4 *>(a.res + row * C) + v * 32 + lane);
+        }
+    };
+    if (warp0 < a.rows) fetch(warp0);
     for (int64_t row = warp0; row < a.rows; row += nwarps) {
-        const uint4 *xr = reinterpret_cast<const uint4 *>(a.x + row * C);
+        uint4 cx[VEC], cr[VEC];
+#pragma unroll
+        for (int v = 0; v < VEC; ++v) cx[v] = nx[v], cr[v] = nr[v];
+        if (row + nwarps < a.rows) fetch(row + nwarps);
         float z[VEC][8];
         float s = 0.f;
 #pragma unroll
         for (int v = 0; v < VEC; ++v) {
-            unpack8(xr[v * 32 + lane], z[v]);
+            unpack8(cx[v], z[v]);
             if (a.thr16) {
                 const uint32_t keep = keep8(a.seed, (uint64_t)row * (C / 8) + v * 32 + lane, a.thr16);
 #pragma unroll
@@ -98,7 +117,7 @@ __global__ void __launch_bounds__(kThreads) ln_fwd_kernel(const FwdArgs a) {
             }
             if (a.res) {
                 float r[8];
-                unpack8(reinterpret_cast<const uint4 *>(a.res + row * C)[v * 32 + lane], r);
+                unpack8(cr[v], r);
 #pragma unroll
                 for (int i = 0; i < 8; ++i) z[v][i] += r[i];
             }
@@ -146,43 +165,62 @@ struct BwdArgs {
 };
 
 template <int VEC>
-__global__ void __launch_bounds__(kThreads) ln_bwd_kernel(const BwdArgs a) {
+__global__ void __launch_bounds__(kThreads, VEC <= 3 ? 2 : 1) ln_bwd_kernel(const BwdArgs a) {
     constexpr int C = VEC * 256;
     __shared__ float red[kWarps][C];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int64_t warp0 = (int64_t)blockIdx.x * kWarps + warp, nwarps = (int64_t)gridDim.x * kWarps;
-    float g[VEC][8], dg[VEC][8], db[VEC][8];
+    // Register budget (two CTAs per SM => 128 registers): the column partials dg / db stay in fp32 registers, the row itself is
+    // kept as the packed bf16 vectors it arrived in and unpacked twice (before and after the row reduction), gamma is re-read
+    // from L1 per row, and the next row's vectors are requested before this row is reduced.
+    float dg[VEC][8], db[VEC][8];
 #pragma unroll
-    for (int v = 0; v < VEC; ++v) {
-        unpack8(reinterpret_cast<const uint4 *>(a.gamma)[v * 32 + lane], g[v]);
+    for (int v = 0; v < VEC; ++v)
 #pragma unroll
         for (int i = 0; i < 8; ++i) dg[v][i] = db[v][i] = 0.f;
-    }
+    uint4 ny[VEC], nz[VEC];
+    float nmean = 0.f, nrstd = 0.f;
+    auto fetch = [&](int64_t row) {
+#pragma unroll
+        for (int v = 0; v < VEC; ++v) {
+            ny[v] = ldg_stream(reinterpret_cast<const uint4 *>(a.dy + row * C) + v * 32 + lane);
+            nz[v] = ldg_stream(reinterpret_cast<const uint4 *>(a.z + row * C) + v * 32 + lane);
+        }
+        nmean = a.mean[row], nrstd = a.rstd[row];
+    };
+    if (warp0 < a.rows) fetch(warp0);
     for (int64_t row = warp0; row < a.rows; row += nwarps) {
-        const float mean = a.mean[row], rstd = a.rstd[row];
-        float xh[VEC][8], gy[VEC][8];
+        uint4 cy[VEC], cz[VEC];
+#pragma unroll
+        for (int v = 0; v < VEC; ++v) cy[v] = ny[v], cz[v] = nz[v];
+        const float mean = nmean, rstd = nrstd;
+        if (row + nwarps < a.rows) fetch(row + nwarps);
         float s1 = 0.f, s2 = 0.f;
 #pragma unroll
         for (int v = 0; v < VEC; ++v) {
-            float dy[8];
-            unpack8(reinterpret_cast<const uint4 *>(a.dy + row * C)[v * 32 + lane], dy);
-            unpack8(reinterpret_cast<const uint4 *>(a.z + row * C)[v * 32 + lane], xh[v]);
+            float dy[8], xh[8], g[8];
+            unpack8(cy[v], dy);
+            unpack8(cz[v], xh);
+            unpack8(__ldg(reinterpret_cast<const uint4 *>(a.gamma) + v * 32 + lane), g);
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
-                xh[v][i] = (xh[v][i] - mean) * rstd;
-                dg[v][i] = fmaf(dy[i], xh[v][i], dg[v][i]);
+                xh[i] = (xh[i] - mean) * rstd;
+                dg[v][i] = fmaf(dy[i], xh[i], dg[v][i]);
                 db[v][i] += dy[i];
-                gy[v][i] = dy[i] * g[v][i];
-                s1 += gy[v][i];
-                s2 = fmaf(gy[v][i], xh[v][i], s2);
+                const float gy = dy[i] * g[i];
+                s1 += gy;
+                s2 = fmaf(gy, xh[i], s2);
             }
         }
         const float c1 = warp_sum(s1) * (1.f / C), c2 = warp_sum(s2) * (1.f / C);
 #pragma unroll
         for (int v = 0; v < VEC; ++v) {
-            float dz[8];
+            float dy[8], xh[8], g[8], dz[8];
+            unpack8(cy[v], dy);
+            unpack8(cz[v], xh);
+            unpack8(__ldg(reinterpret_cast<const uint4 *>(a.gamma) + v * 32 + lane), g);
 #pragma unroll
-            for (int i = 0; i < 8; ++i) dz[i] = (gy[v][i] - c1 - xh[v][i] * c2) * rstd;
+            for (int i = 0; i < 8; ++i) dz[i] = (dy[i] * g[i] - c1 - (xh[i] - mean) * rstd * c2) * rstd;
             if (a.dres) reinterpret_cast<uint4 *>(a.dres + row * C)[v * 32 + lane] = pack8(dz);
             if (a.dx) {
                 if (a.thr16) {

@@ -17,6 +17,8 @@ from . import _lib
 
 # When set to a list, the attention wrappers append (kind, start_event, end_event, B, H, T) around
 # their C-ABI call on the current stream: bench.py derives the kernels' live in-step durations from it.
+# The LayerNorm wrappers append ("ln_fwd" | "ln_bwd", start, end, rows, C, flags) the same way
+# (ln_fwd flags: 2 = has residual, 1 = writes z; ln_bwd flags = number of gradient tensors written).
 ATTN_EVENTS = None
 
 
@@ -333,7 +335,7 @@ class _DropoutAddLayerNorm(torch.autograd.Function):
         mean = torch.empty(rows, dtype=torch.float32, device=x.device)
         rstd = torch.empty(rows, dtype=torch.float32, device=x.device)
         w, b = weight.detach().contiguous(), bias.detach().contiguous()
-        with torch.cuda.device(x.device):
+        with torch.cuda.device(x.device), _timed("ln_fwd", rows, C, (2 if r2 is not None else 0) + (1 if need_z else 0)):
             _lib.check(lib.mdt_dropout_add_ln_fwd(_lib.ptr(x2), _lib.ptr(r2), _lib.ptr(w), _lib.ptr(b), _lib.ptr(y), _lib.ptr(z),
                                                   _lib.ptr(mean), _lib.ptr(rstd), rows, C, float(p), int(seed), float(eps),
                                                   _lib.stream()), "mdt_dropout_add_ln_fwd")
@@ -359,7 +361,7 @@ class _DropoutAddLayerNorm(torch.autograd.Function):
         dbeta = torch.zeros(C, dtype=torch.float32, device=gy.device)
         if dx is None and dres is None:
             dres = torch.empty_like(gy2)
-        with torch.cuda.device(gy.device):
+        with torch.cuda.device(gy.device), _timed("ln_bwd", rows, C, (1 if dx is not None else 0) + (1 if dres is not None else 0)):
             _lib.check(lib.mdt_dropout_add_ln_bwd(_lib.ptr(gy2), _lib.ptr(z), _lib.ptr(mean), _lib.ptr(rstd), _lib.ptr(w),
                                                   _lib.ptr(dx), _lib.ptr(dres), _lib.ptr(dgamma), _lib.ptr(dbeta), rows, C,
                                                   float(p), int(seed), _lib.stream()), "mdt_dropout_add_ln_bwd")
