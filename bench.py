@@ -45,6 +45,10 @@ def parse_args():
     ap.add_argument("--image-frac", type=float, default=0.10)
     ap.add_argument("--pool", type=int, default=2, help="distinct pre-packed host batches cycled through")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--prep", action="store_true",
+                    help="configs[1] instead of the training step: Floyd-Warshall sweep (16-512 nodes, batch 256) and "
+                         "GraphAttnBias GB/s, one JSON line per case, the CPU reference timed beside each APSP size")
+    ap.add_argument("--prep-json", default=None)
     return ap.parse_args()
 
 
@@ -152,6 +156,45 @@ def cpu_reference_arm(nodes: int, steps: int, warmup: int, image_frac: float, dr
     return dict(value=steps / dt, unit=UNIT, cores=cores, kind="port",
                 sample=f"{steps} steps of 1 graph x {nodes} comments (same model, fp32, torch CPU, {cores} threads): "
                        f"collate + fwd + bwd + AdamW"), dt / steps * 1e3
+
+
+def run_prep(args):
+    """BASELINE.json configs[1] + GraphAttnBias: benchmarks/prep_microbench.py with the CPU reference beside it."""
+    sys.path.insert(0, os.path.join(ROOT, "benchmarks"))
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import prep_microbench as pm
+
+    ref = None
+    try:  # the reference's own Cython floyd_warshall when oracle/_ref was built (it travels with the snapshot)
+        import build_ref
+
+        ref = build_ref.load_ref_algos(build=False)
+    except Exception:
+        ref = None
+    import mdt_oracle as orc  # CPU-baseline leg (and the bit-exact check of the timed sample)
+
+    from multimodaldiscussiontransformer_b200.data import algos
+    import torch
+
+    def cpu_fn(adj_np):
+        n = adj_np.shape[1]
+        k = max(1, min(adj_np.shape[0], int(1.5e9 / n ** 3)))  # bounded sample: <= ~1.5 G relaxations per size
+        sample = adj_np[:k].astype("int64")
+        t0 = time.perf_counter()
+        if ref is not None:
+            outs = [ref.floyd_warshall(sample[i]) for i in range(k)]
+            kind = "reference"
+        else:
+            outs = [orc.floyd_warshall(sample[i]) for i in range(k)]
+            kind = "port"
+        dt = time.perf_counter() - t0
+        M, path = algos.floyd_warshall_batched(torch.from_numpy(adj_np[:k]).cuda(), True)
+        exact = all((M[i].cpu().numpy() == outs[i][0]).all() and (path[i].cpu().numpy() == outs[i][1]).all()
+                    for i in range(k))
+        return dict(graphs_per_s=k / dt, ms_per_graph=dt / k * 1e3, cores=1, kind=kind, sample=f"{k} graphs of {n} nodes",
+                    bit_exact_vs_gpu=bool(exact))
+
+    pm.main(cpu_fn=cpu_fn, argv=["--json", args.prep_json] if args.prep_json else [])
 
 
 def run_reference(args):
@@ -384,5 +427,7 @@ if __name__ == "__main__":
     a = parse_args()
     if a.impl == "reference":
         run_reference(a)
+    elif a.prep:
+        run_prep(a)
     else:
         run_b200(a)
