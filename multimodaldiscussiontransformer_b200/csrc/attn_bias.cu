@@ -133,8 +133,28 @@ __global__ void __launch_bounds__(kBiasThreads)
 }
 
 // backward: grad_table[c][h] += sum of grad_out over positions with spatial index c (c != 0),
-// grad_virt[h] += sum over the graph-token row and column.  Reads grad_out once; per-thread
-// private shared-memory bins for the first 32 indices (mDT uses 1..21), global atomics above.
+// grad_virt[h] += sum over the graph-token row and column.  Reads grad_out once.  A thread owns 32 positions of the
+// chunk (stride kBiasThreads, so a warp load covers whole sectors); their bin codes are the same for every head, so
+// they are packed into 8 registers once.  Per head the 32 loads are issued back to back, and the next head's loads
+// are in flight while this head's values go into per-thread private shared-memory bins (indices 0..31; mDT uses
+// 1..21) - the first version issued one dependent load per bin update and ran at the latency of 32 x H loads per CTA.
+constexpr int kPerThread = kChunk / kBiasThreads;  // 32
+constexpr uint32_t kCodeVirt = 255, kCodeFar = 254;
+
+template <typename T>
+__device__ __forceinline__ void bias_bwd_load(T (&v)[kPerThread], const T *__restrict__ g, int len, bool full) {
+    if (full) {
+#pragma unroll
+        for (int k = 0; k < kPerThread; ++k) v[k] = __ldcs(g + k * kBiasThreads + threadIdx.x);
+    } else {
+#pragma unroll
+        for (int k = 0; k < kPerThread; ++k) {
+            const int e = k * kBiasThreads + threadIdx.x;
+            v[k] = e < len ? __ldcs(g + e) : from_float<T>(0.f);
+        }
+    }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(kBiasThreads)
     attn_bias_bwd_kernel(const T *__restrict__ go, const int32_t *__restrict__ sp, int H, int N, int num_spatial,
@@ -147,33 +167,47 @@ __global__ void __launch_bounds__(kBiasThreads)
     const int b = blockIdx.y;
     const size_t r0 = (size_t)blockIdx.x * kChunk;
     const int len = (int)min((size_t)kChunk, plane - r0);
+    const bool full = len == kChunk;
     const int32_t *spp = sp + (size_t)b * N * N;
-    for (int e = threadIdx.x; e < len; e += kBiasThreads) {
-        const size_t r = r0 + e;
-        const int i = (int)(r / T_), j = (int)(r - (size_t)i * T_);
-        int c = 0xffff;  // virtual
-        if (i >= 1 && j >= 1) {
-            c = spp[(size_t)(i - 1) * N + (j - 1)];
-            if (c < 0 || c >= num_spatial || c >= 0xfffe) c = 0;  // treated like padding: no gradient
+    const T *g0 = go + (size_t)b * H * plane + r0;
+    T cur[kPerThread];
+    bias_bwd_load(cur, g0, len, full);  // head 0 travels while the codes are built
+    uint32_t cw[kPerThread / 4];
+#pragma unroll
+    for (int k = 0; k < kPerThread; ++k) {
+        const int e = k * kBiasThreads + threadIdx.x;
+        uint32_t byte = 0;  // past the chunk: value 0 into bin 0 (discarded)
+        if (e < len) {
+            const size_t r = r0 + e;
+            const int i = (int)(r / T_), j = (int)(r - (size_t)i * T_);
+            int c = 0xffff;  // virtual
+            if (i >= 1 && j >= 1) {
+                c = spp[(size_t)(i - 1) * N + (j - 1)];
+                if (c < 0 || c >= num_spatial || c >= 0xfffe) c = 0;  // treated like padding: no gradient
+            }
+            code[e] = (uint16_t)c;
+            byte = c < 32 ? (uint32_t)c : (c == 0xffff ? kCodeVirt : kCodeFar);
         }
-        code[e] = (uint16_t)c;
+        if ((k & 3) == 0) cw[k >> 2] = 0;
+        cw[k >> 2] |= byte << (8 * (k & 3));
     }
-    __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     for (int h = 0; h < H; ++h) {
-        const T *g = go + ((size_t)b * H + h) * plane + r0;
+        T nxt[kPerThread];
+        if (h + 1 < H) bias_bwd_load(nxt, g0 + (size_t)(h + 1) * plane, len, full);
 #pragma unroll
         for (int c = 0; c < 32; ++c) bins[c * kBiasThreads + threadIdx.x] = 0.f;
         float vacc = 0.f;
-        for (int e = threadIdx.x; e < len; e += kBiasThreads) {
-            const int c = code[e];
-            const float v = to_float(g[e]);
+#pragma unroll
+        for (int k = 0; k < kPerThread; ++k) {
+            const uint32_t c = (cw[k >> 2] >> (8 * (k & 3))) & 255u;
+            const float v = to_float(cur[k]);
             if (c < 32)
                 bins[c * kBiasThreads + threadIdx.x] += v;
-            else if (c == 0xffff)
+            else if (c == kCodeVirt)
                 vacc += v;
             else
-                atomicAdd(&grad_table[(size_t)c * H + h], v);
+                atomicAdd(&grad_table[(size_t)code[k * kBiasThreads + threadIdx.x] * H + h], v);
         }
         __syncthreads();
         for (int c = warp; c < 32; c += kBiasThreads / 32) {
@@ -188,6 +222,10 @@ __global__ void __launch_bounds__(kBiasThreads)
         for (int o = 16; o > 0; o >>= 1) vacc += __shfl_xor_sync(0xffffffffu, vacc, o);
         if (lane == 0 && vacc != 0.f) atomicAdd(&grad_virt[h], vacc);
         __syncthreads();
+        if (h + 1 < H) {
+#pragma unroll
+            for (int k = 0; k < kPerThread; ++k) cur[k] = nxt[k];
+        }
     }
 }
 

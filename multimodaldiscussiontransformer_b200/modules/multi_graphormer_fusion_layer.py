@@ -85,22 +85,29 @@ class _SeqLens:
 _FLASH = None
 
 
-def _varlen_attention(q, k, v, pack, dropout_p: float):
-    """Self-attention over the packed sequences: ``[total, H, d]`` -> ``[total, H, d]`` (library kernel: flash-attn)."""
+def _varlen_attention(qkv, pack, dropout_p: float):
+    """Self-attention over the packed sequences: ``[total, 3, H, d]`` -> ``[total, H, d]`` (library kernel: flash-attn;
+    the packed-QKV entry point returns one ``[total, 3, H, d]`` gradient, so autograd never re-assembles three slices)."""
     global _FLASH
     if _FLASH is None:
-        from flash_attn import flash_attn_varlen_func
-        _FLASH = flash_attn_varlen_func
-    return _FLASH(q, k, v, pack.cu_seqlens, pack.cu_seqlens, pack.max_seqlen, pack.max_seqlen, dropout_p=dropout_p)
+        from flash_attn import flash_attn_varlen_qkvpacked_func
+        _FLASH = flash_attn_varlen_qkvpacked_func
+    return _FLASH(qkv, pack.cu_seqlens, pack.max_seqlen, dropout_p=dropout_p)
 
 
 def packed_bert_layer(layer, x: torch.Tensor, pack) -> torch.Tensor:
-    """Hugging Face ``BertLayer`` arithmetic (post-LN block, same parameters, same dropout rates) on packed tokens."""
+    """Hugging Face ``BertLayer`` arithmetic (post-LN block, same parameters, same dropout rates) on packed tokens.
+
+    The three projections run as ONE GEMM over the row-concatenated ``query / key / value`` weights (the parameters stay
+    separate, state-dict keys unchanged): ``x`` is read once, and the backward has one input-gradient GEMM and one
+    bias-gradient reduction instead of three of each plus two gradient-accumulation adds over ``[total, C]``."""
     att, sa = layer.attention, layer.attention.self
     H = sa.num_attention_heads
     d = x.shape[-1] // H
-    q, k, v = (f(x).view(-1, H, d) for f in (sa.query, sa.key, sa.value))
-    ctx = _varlen_attention(q, k, v, pack, sa.dropout.p if layer.training else 0.0).reshape(x.shape)
+    w = torch.cat([sa.query.weight, sa.key.weight, sa.value.weight], 0)
+    b = torch.cat([sa.query.bias, sa.key.bias, sa.value.bias], 0)
+    qkv = torch.nn.functional.linear(x, w, b).view(-1, 3, H, d)
+    ctx = _varlen_attention(qkv, pack, sa.dropout.p if layer.training else 0.0).reshape(x.shape)
     if x.dtype == torch.bfloat16 and x.shape[-1] in (256, 512, 768, 1024):
         # dense -> dropout -> + residual -> LayerNorm tails in one pass each way (libmdt_b200, csrc/layernorm.cu)
         ln1, ln2 = att.output.LayerNorm, layer.output.LayerNorm
@@ -111,6 +118,31 @@ def packed_bert_layer(layer, x: torch.Tensor, pack) -> torch.Tensor:
     h = att.output.LayerNorm(att.output.dropout(att.output.dense(ctx)) + x)
     inter = layer.intermediate(h)
     return layer.output.LayerNorm(layer.output.dropout(layer.output.dense(inter)) + h)
+
+
+class _PrependTokens(torch.autograd.Function):
+    """``cat([bottle_neck, hidden], dim=1)`` as two strided copies into one buffer.  ``hidden`` is the ``[:, nb:]`` view of
+    the previous layer's output, and ``torch.cat`` serves a non-contiguous input with its scalar (non-vectorised) copy
+    kernel (0.5 TB/s on the ViT tokens); the gradients are the two views of the incoming gradient, as in ``cat``."""
+
+    @staticmethod
+    def forward(ctx, bn, hidden):
+        nb = bn.shape[1]
+        out = hidden.new_empty(hidden.shape[0], nb + hidden.shape[1], hidden.shape[2])
+        out[:, :nb].copy_(bn)
+        out[:, nb:].copy_(hidden)
+        ctx.nb = nb
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        return g[:, :ctx.nb], g[:, ctx.nb:]
+
+
+def prepend_tokens(bn: torch.Tensor, hidden: torch.Tensor) -> torch.Tensor:
+    if hidden.is_cuda and not hidden.is_contiguous():
+        return _PrependTokens.apply(bn, hidden)
+    return torch.cat([bn, hidden], dim=1)
 
 
 class FusedLayerNorm(nn.LayerNorm):
@@ -179,7 +211,7 @@ class GraphFusionLayer(nn.Module):
         bottle_neck_output = x_packed.index_select(0, pack.bn_rows).view(-1, nb, C)
         if vit_hidden_states is not None:
             rows = image_rows(x_image_indexes)
-            vit_out = self.vit_forward(torch.cat([bottle_neck.index_select(0, rows), vit_hidden_states], dim=1))
+            vit_out = self.vit_forward(prepend_tokens(bottle_neck.index_select(0, rows), vit_hidden_states))
             vit_hidden_output = vit_out[:, nb:]
             mixed = (vit_out[:, :nb] + bottle_neck_output.index_select(0, rows)) / 2
             bottle_neck_output = bottle_neck_output.index_copy(0, rows, mixed)
