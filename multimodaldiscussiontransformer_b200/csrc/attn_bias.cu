@@ -139,7 +139,8 @@ __global__ void __launch_bounds__(kBiasThreads)
 // are in flight while this head's values go into per-thread private shared-memory bins (indices 0..31; mDT uses
 // 1..21) - the first version issued one dependent load per bin update and ran at the latency of 32 x H loads per CTA.
 constexpr int kPerThread = kChunk / kBiasThreads;  // 32
-constexpr uint32_t kCodeVirt = 255, kCodeFar = 254;
+constexpr int kBins = 33;                          // spatial indices 0..31 + the graph-token (virtual distance) bin
+constexpr uint32_t kCodeVirt = 32, kCodeFar = 254;
 
 template <typename T>
 __device__ __forceinline__ void bias_bwd_load(T (&v)[kPerThread], const T *__restrict__ g, int len, bool full) {
@@ -161,7 +162,7 @@ __global__ void __launch_bounds__(kBiasThreads)
                          float *__restrict__ grad_table, float *__restrict__ grad_virt) {
     extern __shared__ __align__(16) uint8_t smem[];
     uint16_t *code = reinterpret_cast<uint16_t *>(smem);                              // [kChunk]
-    float *bins = reinterpret_cast<float *>(smem + kChunk * sizeof(uint16_t));        // [32][kBiasThreads]
+    float *bins = reinterpret_cast<float *>(smem + kChunk * sizeof(uint16_t));        // [kBins][kBiasThreads]
     const int T_ = N + 1;
     const size_t plane = (size_t)T_ * T_;
     const int b = blockIdx.y;
@@ -196,31 +197,30 @@ __global__ void __launch_bounds__(kBiasThreads)
         T nxt[kPerThread];
         if (h + 1 < H) bias_bwd_load(nxt, g0 + (size_t)(h + 1) * plane, len, full);
 #pragma unroll
-        for (int c = 0; c < 32; ++c) bins[c * kBiasThreads + threadIdx.x] = 0.f;
-        float vacc = 0.f;
+        for (int c = 0; c < kBins; ++c) bins[c * kBiasThreads + threadIdx.x] = 0.f;
 #pragma unroll
         for (int k = 0; k < kPerThread; ++k) {
             const uint32_t c = (cw[k >> 2] >> (8 * (k & 3))) & 255u;
             const float v = to_float(cur[k]);
-            if (c < 32)
+            if (c != kCodeFar)  // the only branch: no mDT batch takes the far side (indices >= 32)
                 bins[c * kBiasThreads + threadIdx.x] += v;
-            else if (c == kCodeVirt)
-                vacc += v;
             else
                 atomicAdd(&grad_table[(size_t)code[k * kBiasThreads + threadIdx.x] * H + h], v);
         }
         __syncthreads();
-        for (int c = warp; c < 32; c += kBiasThreads / 32) {
+        for (int c = warp; c < kBins; c += kBiasThreads / 32) {
             float s = 0.f;
 #pragma unroll
             for (int q = 0; q < kBiasThreads / 32; ++q) s += bins[c * kBiasThreads + q * 32 + lane];
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-            if (lane == 0 && c != 0 && c < num_spatial && s != 0.f) atomicAdd(&grad_table[(size_t)c * H + h], s);
+            if (lane == 0 && s != 0.f) {
+                if (c == (int)kCodeVirt)
+                    atomicAdd(&grad_virt[h], s);
+                else if (c != 0 && c < num_spatial)
+                    atomicAdd(&grad_table[(size_t)c * H + h], s);
+            }
         }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) vacc += __shfl_xor_sync(0xffffffffu, vacc, o);
-        if (lane == 0 && vacc != 0.f) atomicAdd(&grad_virt[h], vacc);
         __syncthreads();
         if (h + 1 < H) {
 #pragma unroll
@@ -264,7 +264,7 @@ extern "C" int mdt_attn_bias_bwd(const void *grad_out, const int32_t *spatial_po
     MDT_REQUIRE(dtype == MDT_F32 || dtype == MDT_BF16, "unknown dtype %d", dtype);
     const size_t plane = (size_t)(N + 1) * (N + 1);
     dim3 grid((unsigned)((plane + kChunk - 1) / kChunk), B);
-    const size_t smem = kChunk * sizeof(uint16_t) + 32 * kBiasThreads * sizeof(float);
+    const size_t smem = kChunk * sizeof(uint16_t) + (size_t)kBins * kBiasThreads * sizeof(float);
     if (dtype == MDT_F32) {
         MDT_CHECK_CUDA(cudaFuncSetAttribute(attn_bias_bwd_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attn_bias_bwd_kernel<float><<<grid, kBiasThreads, smem, as_stream(stream)>>>((const float *)grad_out, spatial_pos, H, N,
