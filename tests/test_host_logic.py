@@ -160,3 +160,19 @@ def test_text_pack_round_trip_and_host_lengths():
     # a mask with a hole is not a prefix: the collator then does not offer the packed path
     items[0].x["attention_mask"][0, 1] = 0
     assert not HostBatch(items, pin=False).text_prefix
+
+
+def test_prepend_tokens_equals_cat_with_gradients():
+    """The strided-copy prepend of the bottleneck tokens (fusion layer, ViT side) is ``torch.cat`` value- and gradient-wise
+    (multi_graphormer_fusion_layer.py:57 of the reference concatenates the same two tensors)."""
+    from multimodaldiscussiontransformer_b200.modules.multi_graphormer_fusion_layer import _PrependTokens, prepend_tokens
+
+    g = torch.Generator().manual_seed(3)
+    bn = torch.randn(5, 4, 16, generator=g, requires_grad=True)
+    full = torch.randn(5, 4 + 9, 16, generator=g, requires_grad=True)
+    hidden = full[:, 4:]  # the non-contiguous view a fusion layer hands to the next one
+    got, ref = _PrependTokens.apply(bn, hidden), torch.cat([bn, hidden], dim=1)
+    assert torch.equal(got, ref) and torch.equal(prepend_tokens(bn, hidden), ref)
+    go = torch.randn(ref.shape, generator=g)
+    for a, b in zip(torch.autograd.grad(got, (bn, full), go), torch.autograd.grad(ref, (bn, full), go)):
+        assert torch.equal(a, b)
