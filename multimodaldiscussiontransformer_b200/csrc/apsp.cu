@@ -16,6 +16,7 @@
 // smaller than 128 nodes share a CTA (several graphs per block) so small batches still
 // fill the SMs.
 #include <cooperative_groups.h>
+#include <type_traits>
 
 #include "common.cuh"
 
@@ -133,15 +134,13 @@ template <int CLUSTER> __global__ void __launch_bounds__(1024, 1) apsp_tile_kern
         }
     }
 
-    // publish row kk / column kk for the step that uses them
-    auto publish = [&](int kk, int buf) {
-        if (!active) return;
+    // publish row kk / column kk for the step that uses them.  kk is uniform over the CTA, so the register that holds
+    // row / column (kk & 7) of a thread's 8x8 tile is picked by a uniform switch over statically indexed copies: a
+    // run-time index into m[][] put the tile into local memory and cost ~200 instructions per k step.
+    auto publish_sel = [&](auto sel_c, int kk, int buf) {
+        constexpr int SEL = decltype(sel_c)::value;
         if ((kk >> 3) == trow) {
-            const int rsel = kk & 7;
-            uint4 v = make_uint4(0, 0, 0, 0);
-#pragma unroll
-            for (int rr = 0; rr < 8; ++rr)
-                if (rr == rsel) v = make_uint4(m[rr][0], m[rr][1], m[rr][2], m[rr][3]);
+            const uint4 v = make_uint4(m[SEL][0], m[SEL][1], m[SEL][2], m[SEL][3]);
             if constexpr (CLUSTER > 1) {
                 cg::cluster_group cl = cg::this_cluster();
 #pragma unroll
@@ -154,22 +153,25 @@ template <int CLUSTER> __global__ void __launch_bounds__(1024, 1) apsp_tile_kern
             }
         }
         if ((kk >> 3) == tcol) {
-            const int csel = kk & 7;
+            constexpr int W = SEL >> 1;
+            constexpr uint32_t SELECTOR = (SEL & 1) ? 0x7632u : 0x5410u;  // {hi.half, lo.half} of the chosen column
             uint32_t out[4];
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                uint32_t lo = 0, hi = 0;
-#pragma unroll
-                for (int w = 0; w < 4; ++w) {
-                    if (w == (csel >> 1)) {
-                        lo = m[2 * q][w];
-                        hi = m[2 * q + 1][w];
-                    }
-                }
-                const int sh = (csel & 1) * 16;
-                out[q] = ((lo >> sh) & 0xffffu) | (((hi >> sh) & 0xffffu) << 16);
-            }
+            for (int q = 0; q < 4; ++q) out[q] = __byte_perm(m[2 * q][W], m[2 * q + 1][W], SELECTOR);
             *reinterpret_cast<uint4 *>(colbuf + buf * rt * 8 + trow_l * 8) = make_uint4(out[0], out[1], out[2], out[3]);
+        }
+    };
+    auto publish = [&](int kk, int buf) {
+        if (!active) return;
+        switch (kk & 7) {
+            case 0: publish_sel(std::integral_constant<int, 0>{}, kk, buf); break;
+            case 1: publish_sel(std::integral_constant<int, 1>{}, kk, buf); break;
+            case 2: publish_sel(std::integral_constant<int, 2>{}, kk, buf); break;
+            case 3: publish_sel(std::integral_constant<int, 3>{}, kk, buf); break;
+            case 4: publish_sel(std::integral_constant<int, 4>{}, kk, buf); break;
+            case 5: publish_sel(std::integral_constant<int, 5>{}, kk, buf); break;
+            case 6: publish_sel(std::integral_constant<int, 6>{}, kk, buf); break;
+            default: publish_sel(std::integral_constant<int, 7>{}, kk, buf); break;
         }
     };
     auto barrier = [&]() {
