@@ -38,7 +38,15 @@ extern "C" {
 #define MDT_SPATIAL_CANTOR 0 /* mDT: Cantor-paired (hops up, hops down), pre_processing.py:31-53 */
 #define MDT_SPATIAL_SPD 1    /* upstream Graphormer: shortest-path distance itself */
 
-/* bias-code bytes consumed by the fused attention (bias synthesised in-kernel) */
+/* bias-code bytes consumed by the fused attention (bias synthesised in-kernel).
+ * Legal bytes: spatial codes 0..MDT_CODE_SPATIAL_MAX, MDT_CODE_VIRTUAL, MDT_CODE_MASKED.  Bytes 62..253 are
+ * RESERVED: the persistent forward indexes a 64-entry table by (code & 63), so they would alias; callers must not
+ * pass them (mdt_collate_graphs never emits them: Cantor codes are <= 21, SPD codes <= spatial_pos_max, which it
+ * limits to MDT_CODE_GRAD_MAX when codes are requested).  grad_lut is exact for codes 0..MDT_CODE_GRAD_MAX and
+ * MDT_CODE_VIRTUAL; gradients of spatial codes above MDT_CODE_GRAD_MAX are accumulated into entry MDT_CODE_GRAD_MAX
+ * (use the materialised bias for wider tables). */
+#define MDT_CODE_SPATIAL_MAX 61
+#define MDT_CODE_GRAD_MAX 22
 #define MDT_CODE_VIRTUAL 254 /* graph-token virtual distance t[h], graphormer_layers.py:105-106 */
 #define MDT_CODE_MASKED 255  /* -inf */
 
@@ -88,7 +96,9 @@ int mdt_gen_edge_input(const int64_t *path, const int64_t *edge_feat, int B, int
  *                     row/column, MDT_CODE_MASKED where attn_bias is -inf
  *   adj_workspace     [B,N8,N8] uint8 scratch, N8 = N rounded up to 8
  *   The hop pairs of the reference's distance_matrix are recovered from the tree rooted at
- *   node 0: depth = M[0,:], up = (M + d_i - d_j)/2, down = (M - d_i + d_j)/2.
+ *   node 0: depth = M[0,:], up = (M + d_i - d_j)/2, down = (M - d_i + d_j)/2.  This equals the reference's
+ *   distance_matrix for undirected trees rooted at node 0 only (MDT_SPATIAL_CANTOR); the host side
+ *   (data/collator.py: check_discussion_tree) refuses anything else.  Edge endpoints must lie inside their graph.
  * ------------------------------------------------------------------------------------ */
 int mdt_collate_graphs(const int32_t *edge_src, const int32_t *edge_dst, const int32_t *edge_offsets,
                        const int32_t *n_nodes, int B, int N, int spatial_pos_max, int flavour,

@@ -17,6 +17,7 @@ LIB_PATH = os.path.join(_HERE, "libmdt_b200.so")
 F32, BF16 = 0, 1
 SPATIAL_CANTOR, SPATIAL_SPD = 0, 1
 CODE_VIRTUAL, CODE_MASKED = 254, 255
+CODE_SPATIAL_MAX, CODE_GRAD_MAX = 61, 22  # include/mdt_b200.h: spatial codes the fused kernels index / bin gradients for
 
 _lib = None
 

@@ -1,6 +1,7 @@
 """``node_cross_entropy`` criterion (mDT/src/criterions/hatespeech_loss.py:23-182): class-weighted
 cross entropy, summed over the labelled comments, plus the counters behind accuracy / precision /
-recall / F1.  The reference's device->host->device round trip of the logits (:95) is gone."""
+recall / F1.  The reference's device->host->device round trip of the logits (:95) is gone, and so is
+the boolean-mask gather: the forward does not synchronise with the host."""
 
 from __future__ import annotations
 
@@ -31,17 +32,28 @@ class GraphPredictionNodeCrossEntropy(FairseqCriterion):
         bd = sample["net_input"]["batched_data"]
         num_comments = bd["x"].shape[1]
         comment_logits, _ = model(**sample["net_input"])
-        logits = comment_logits[bd["y_mask"]].float()
+        # The reference indexes ``comment_logits[y_mask]`` (:95-99), a boolean-mask gather that costs a device->host
+        # sync.  Same numbers without it: every comment gets the label of its rank among the labelled ones, the
+        # per-comment losses / counters are masked and summed.  ``sample_size`` = number of labels = ``len(logits)`` (:97).
+        mask = bd["y_mask"].reshape(-1).bool()
         targets = torch.flatten(bd["y"]).long()
-        sample_size = logits.shape[0]
+        sample_size = int(targets.numel())
+        logits = comment_logits.float()
+        if sample_size == 0:
+            tgt_all = torch.zeros(mask.shape[0], dtype=torch.long, device=mask.device)
+        else:
+            rank = (torch.cumsum(mask.to(torch.int32), 0) - 1).clamp_(0, sample_size - 1)
+            tgt_all = targets[rank.long()]
+        weight = self.weight.to(logits.device)
         with torch.no_grad():
             pred = torch.argmax(logits, dim=-1)
-            ncorrect = (pred == targets).sum()
-            num_positive_correct = ((pred == targets) & (pred == 1)).sum()
-            total_positive = (targets == 1).sum()
-            num_pred_positive = (pred == 1).sum()
-        loss = F.cross_entropy(logits, targets, reduction="sum" if reduce else "none",
-                               weight=self.weight.to(logits.device))
+            hit = (pred == tgt_all) & mask
+            ncorrect = hit.sum()
+            num_positive_correct = (hit & (pred == 1)).sum()
+            total_positive = ((tgt_all == 1) & mask).sum()
+            num_pred_positive = ((pred == 1) & mask).sum()
+        per_comment = F.cross_entropy(logits, tgt_all, reduction="none", weight=weight) * mask.to(logits.dtype)
+        loss = per_comment.sum() if reduce else per_comment
         logging_output = {"loss": loss.data, "sample_size": sample_size, "nsentences": sample_size, "ntokens": num_comments,
                           "ncorrect": ncorrect, "num_positive_correct": num_positive_correct,
                           "total_positive": total_positive, "num_pred_positive": num_pred_positive}

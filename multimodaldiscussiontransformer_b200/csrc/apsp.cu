@@ -357,13 +357,14 @@ __global__ void __launch_bounds__(1024, 1)
 // whose final distance is either reset to 510 (path forced to 510) or later improved again
 // below 510 (path overwritten by that later k).
 
-__global__ void edges_to_adj_kernel(const int32_t *src, const int32_t *dst, const int32_t *offsets, int B, int n8x8,
-                                    uint8_t *adj) {
+__global__ void edges_to_adj_kernel(const int32_t *src, const int32_t *dst, const int32_t *offsets, const int32_t *n_nodes,
+                                    int B, int n8x8, uint8_t *adj) {
     const int b = blockIdx.y;
     const int e0 = offsets[b], e1 = offsets[b + 1];
+    const int nb = min(n_nodes[b], n8x8);  // endpoints outside the graph are dropped: padded nodes must stay isolated
     for (int e = e0 + blockIdx.x * blockDim.x + threadIdx.x; e < e1; e += gridDim.x * blockDim.x) {
         const int s = src[e], d = dst[e];
-        if (s >= 0 && d >= 0 && s < n8x8 && d < n8x8) adj[((size_t)b * n8x8 + s) * n8x8 + d] = 1;  // pre_processing.py:28-29
+        if (s >= 0 && d >= 0 && s < nb && d < nb) adj[((size_t)b * n8x8 + s) * n8x8 + d] = 1;  // pre_processing.py:28-29
     }
 }
 
@@ -514,10 +515,13 @@ extern "C" int mdt_collate_graphs(const int32_t *edge_src, const int32_t *edge_d
     MDT_REQUIRE(flavour == MDT_SPATIAL_CANTOR || flavour == MDT_SPATIAL_SPD, "unknown flavour %d", flavour);
     MDT_REQUIRE(bias_dtype == MDT_F32 || bias_dtype == MDT_BF16, "unknown dtype %d", bias_dtype);
     MDT_REQUIRE(bias_code == nullptr || code_pitch >= N + 1, "code_pitch %d < T=%d", code_pitch, N + 1);
+    // unmasked codes of the SPD flavour reach spatial_pos_max; the fused attention bins LUT gradients for codes 0..22
+    MDT_REQUIRE(bias_code == nullptr || flavour != MDT_SPATIAL_SPD || spatial_pos_max <= MDT_CODE_GRAD_MAX,
+                "bias codes of the SPD flavour need spatial_pos_max <= %d (got %d)", MDT_CODE_GRAD_MAX, spatial_pos_max);
     const int n8x8 = ((N + 7) / 8) * 8;
     cudaStream_t s = as_stream(stream);
     MDT_CHECK_CUDA(cudaMemsetAsync(adj_workspace, 0, (size_t)B * n8x8 * n8x8, s));
-    edges_to_adj_kernel<<<dim3(4, B), 256, 0, s>>>(edge_src, edge_dst, edge_offsets, B, n8x8, adj_workspace);
+    edges_to_adj_kernel<<<dim3(4, B), 256, 0, s>>>(edge_src, edge_dst, edge_offsets, n_nodes, B, n8x8, adj_workspace);
     MDT_CHECK_CUDA(cudaGetLastError());
     ApspParams p = {};
     p.adj = adj_workspace;

@@ -495,11 +495,8 @@ template <int MODE>
 static int launch_bwd(const CUtensorMap &mq, const CUtensorMap &mk, const CUtensorMap &mv, const CUtensorMap &mdo,
                       const CUtensorMap &mc, const BwdArgs &a, cudaStream_t st) {
     const int smem = kBwdSmemBase + 1024 + (MODE == kBiasCode ? kBwdCodeBytes : 0) + ((MODE == kBiasCode && a.grad_lut) ? kBwdBinsBytes : 0);
-    static int configured = 0;
-    if (configured < smem) {
-        MDT_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        configured = smem;
-    }
+    // per launch: the attribute is per device and the call is cheap (no cache keyed on the wrong device)
+    MDT_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     dim3 grid((a.Tmain + kTile - 1) / kTile, a.H, a.B);
     attn_bwd_kernel<MODE><<<grid, kBwdThreads, smem, st>>>(mq, mk, mv, mdo, mc, a);
     MDT_CHECK_CUDA(cudaGetLastError());

@@ -271,11 +271,7 @@ __global__ void __launch_bounds__(128, 2)
 
 template <int MODE>
 static int launch_fwd(const CUtensorMap &mq, const CUtensorMap &mk, const CUtensorMap &mv, const FwdArgs &a, cudaStream_t st) {
-    static bool configured = false;
-    if (!configured) {
-        MDT_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem));
-        configured = true;
-    }
+    MDT_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem));  // per device
     dim3 grid((a.T + kTile - 1) / kTile, a.H, a.B);
     attn_fwd_kernel<MODE><<<grid, 128, kFwdSmem, st>>>(mq, mk, mv, a);
     MDT_CHECK_CUDA(cudaGetLastError());

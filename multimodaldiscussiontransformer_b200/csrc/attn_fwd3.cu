@@ -494,12 +494,10 @@ __global__ void __launch_bounds__(kF3Threads, 1)
 
 int launch_fwd3(const CUtensorMap &mq, const CUtensorMap &mk, const CUtensorMap &mv, const CUtensorMap &mc, const Fwd2Args &a,
                 cudaStream_t st) {
-    static bool configured = false;
-    if (!configured) {
+    if (a.has_code)  // per launch: the attribute is per device
         MDT_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd3_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kF3Smem));
+    else
         MDT_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd3_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kF3Smem));
-        configured = true;
-    }
     const int nqp = (a.Tmain + 2 * kTile - 1) / (2 * kTile);
     const long long n_items = (long long)a.B * a.H * nqp;
     const int grid = (int)(n_items < (long long)num_sms() ? n_items : (long long)num_sms());

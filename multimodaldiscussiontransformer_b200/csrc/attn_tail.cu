@@ -36,7 +36,7 @@ __global__ void __launch_bounds__(kTailThreads) attn_bwd_tail_k_kernel(const Tai
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int h = blockIdx.x, b = blockIdx.y, T = a.T;
     const bool want_glut = HAS_CODE && a.grad_lut != nullptr;
-    if (HAS_CODE) s_lut[tid] = tid == MDT_CODE_MASKED ? neg_inf() : a.lut[(size_t)h * 256 + tid] * kLog2e;  // log2 domain
+    if (HAS_CODE && tid < 256) s_lut[tid] = tid == MDT_CODE_MASKED ? neg_inf() : a.lut[(size_t)h * 256 + tid] * kLog2e;  // log2 domain
     __syncthreads();
     const uint32_t salt = drop_salt(a.drop, (uint32_t)(b * a.H + h));
     const __nv_bfloat16 *qb = a.q + (size_t)b * a.q_sb + (size_t)h * a.q_sh;

@@ -33,14 +33,16 @@ int require_sm100();
 inline cudaStream_t as_stream(mdt_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
 
 inline int num_sms() {
-    static int n = 0;
-    if (n == 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
+    static int cached[64] = {0};  // per device
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64) dev = 0;
+    if (cached[dev] == 0) {
+        int n = 0;
         cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-        if (n <= 0) n = 148;
+        cached[dev] = n > 0 ? n : 148;
     }
-    return n;
+    return cached[dev];
 }
 
 __device__ __forceinline__ float neg_inf() { return __int_as_float(0xff800000); }

@@ -283,11 +283,7 @@ static int launch_bwd(const BwdArgs &a, cudaStream_t st) {
     constexpr int kGroups = kBwdThreads / 32 / VEC;
     const int64_t want = (a.rows + kGroups - 1) / kGroups, cap = (int64_t)num_sms() * 2;
     const int grid = (int)(want < cap ? want : cap);
-    static bool configured = false;
-    if (!configured) {
-        MDT_CHECK_CUDA(cudaFuncSetAttribute(ln_bwd_kernel<VEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem));
-        configured = true;
-    }
+    MDT_CHECK_CUDA(cudaFuncSetAttribute(ln_bwd_kernel<VEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem));  // per device
     ln_bwd_kernel<VEC><<<grid, kBwdThreads, kBwdSmem, st>>>(a);
     MDT_CHECK_CUDA(cudaGetLastError());
     return MDT_OK;

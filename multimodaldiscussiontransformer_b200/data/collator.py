@@ -1,4 +1,6 @@
-"""Drop-in for ``mDT/src/data/collator.py`` + ``pyg_datasets/pre_processing.py`` on the B200.
+"""``mDT/src/data/collator.py`` + ``pyg_datasets/pre_processing.py`` on the B200 (items are objects with the
+reference item's fields, ``edge_index`` instead of ``distance_matrix``; discussion trees only -- see
+``check_discussion_tree``).
 
 The reference builds ``spatial_pos`` / ``distance`` / ``attn_bias`` / ``in_degree`` per item on
 the CPU with Python ``map`` over N^2 pairs (pre_processing.py:39-56) and pads them per batch
@@ -26,20 +28,87 @@ def _np(a) -> np.ndarray:
     return np.asarray(a)
 
 
+def check_discussion_tree(edge_index, n: int, where: str = "item") -> None:
+    """Raise unless ``edge_index`` ([2, E] int) is an undirected tree over nodes ``0..n-1`` listed in both directions.
+
+    The reference takes ``spatial_pos`` / ``distance`` from the dataset's precomputed ``distance_matrix`` of (hops up,
+    hops down) pairs (hateful_discussions.py:151-159,242-264; pre_processing.py:39-56).  This package re-derives the
+    pairs on the device from shortest-path lengths and depths (depth = distance to node 0, the post), which equals the
+    reference's construction exactly when the graph is a tree rooted at node 0 -- what a discussion is
+    (hateful_discussions.py:116-148).  Anything else (endpoints out of range, self loops, a missing reverse edge,
+    a cycle, several components) would silently give different numbers, so it is refused here, on the host, before any
+    copy is issued."""
+    e = _np(edge_index).reshape(2, -1).astype(np.int64, copy=False)
+    E = e.shape[1]
+    if n < 1:
+        raise ValueError(f"{where}: a discussion needs at least its post (n = {n})")
+    if E != 2 * (n - 1):
+        raise ValueError(f"{where}: a tree over {n} comments has {2 * (n - 1)} directed edges, edge_index has {E}")
+    if E == 0:
+        return
+    src, dst = e[0], e[1]
+    if src.min() < 0 or dst.min() < 0 or src.max() >= n or dst.max() >= n:
+        raise ValueError(f"{where}: edge endpoints must lie in [0, {n})")
+    if np.any(src == dst):
+        raise ValueError(f"{where}: self loops are not part of a discussion tree")
+    fwd, rev = np.sort(src * n + dst), np.sort(dst * n + src)
+    if np.any(fwd[1:] == fwd[:-1]) or not np.array_equal(fwd, rev):
+        raise ValueError(f"{where}: edge_index must list every reply edge once in each direction")
+    # n - 1 undirected edges: connected <=> acyclic <=> tree.  Union-find over the edges.
+    parent = list(range(n))
+
+    def find(a):
+        while parent[a] != a:
+            parent[a] = parent[parent[a]]
+            a = parent[a]
+        return a
+
+    comps = n
+    for a, b in zip(src.tolist(), dst.tolist()):
+        if a < b:
+            ra, rb = find(a), find(b)
+            if ra != rb:
+                parent[ra] = rb
+                comps -= 1
+    if comps != 1:
+        raise ValueError(f"{where}: the reply graph is not connected to the post (node 0): {comps} components")
+
+
 def preprocess_item(item):
     """``preprocess_item`` (pre_processing.py:23-69): nothing is computed on the host any more.
 
     The item keeps ``edge_index`` and ``x``; the O(N^2) tensors are built on the device by
-    ``collator``.  Returned unchanged so dataset wrappers can keep calling it.
+    ``collator``.  Returned unchanged so dataset wrappers can keep calling it.  A precomputed
+    ``item.distance_matrix`` is not read: the hop pairs are re-derived from ``edge_index``, which
+    is exact for trees rooted at node 0 only -- ``HostBatch`` / ``collator`` check that
+    (``check_discussion_tree``) and raise for anything else.
     """
     return item
 
 
 def collate_graph_tensors(edge_index: Sequence[Any], n_nodes: Sequence[int], spatial_pos_max: int, device,
-                          flavour: int = _lib.SPATIAL_CANTOR, bias_dtype=torch.float32, with_code: bool = True):
-    """Edge lists of B graphs -> padded ``spatial_pos``, ``attn_bias``, ``in_degree`` (+ ``bias_code``)."""
+                          flavour: int = _lib.SPATIAL_CANTOR, bias_dtype=torch.float32, with_code: bool = True,
+                          validate: bool = True):
+    """Edge lists of B graphs -> padded ``spatial_pos``, ``attn_bias``, ``in_degree`` (+ ``bias_code``).
+
+    ``flavour=SPATIAL_CANTOR`` (mDT) needs rooted trees (``check_discussion_tree``; ``validate=False`` skips the check
+    for callers that have already made it).  ``flavour=SPATIAL_SPD`` (upstream Graphormer: ``spatial_pos`` = shortest-path
+    length + 1) takes any undirected graph, but endpoints must still lie inside each graph.  Bias codes are one byte:
+    unmasked positions carry ``spatial_pos <= spatial_pos_max``, and the fused attention kernels index a 62-entry
+    table and bin LUT gradients for codes 0..22 (include/mdt_b200.h), so ``with_code`` needs ``spatial_pos_max <= 22``
+    in the SPD flavour (the Cantor flavour never exceeds 21)."""
     lib = _lib.load()
     B = len(n_nodes)
+    if with_code and flavour == _lib.SPATIAL_SPD and spatial_pos_max > _lib.CODE_GRAD_MAX:
+        raise ValueError(f"bias codes of the SPD flavour need spatial_pos_max <= {_lib.CODE_GRAD_MAX} (got {spatial_pos_max}): "
+                         "pass with_code=False and use the materialised GraphAttnBias.forward")
+    for b, (ei, n) in enumerate(zip(edge_index, n_nodes)):
+        if flavour == _lib.SPATIAL_CANTOR and validate:
+            check_discussion_tree(ei, int(n), f"graph {b}")
+        else:
+            e = _np(ei).reshape(2, -1)
+            if e.size and (e.min() < 0 or e.max() >= int(n)):
+                raise ValueError(f"graph {b}: edge endpoints must lie in [0, {int(n)})")
     N = int(max(n_nodes))
     T = N + 1
     srcs, dsts, offs = [], [], [0]
@@ -87,7 +156,8 @@ class HostBatch:
         self.L = int(_np(items[0].x["input_ids"]).shape[1])
         B, N, ns = self.B, self.N, self.sizes
         srcs, dsts, offs = [], [], [0]
-        for it in items:
+        for b, it in enumerate(items):
+            check_discussion_tree(it.edge_index, ns[b], f"item {b} (idx {int(it.idx)})")
             e = _np(it.edge_index).astype(np.int32, copy=False).reshape(2, -1)
             srcs.append(e[0])
             dsts.append(e[1])

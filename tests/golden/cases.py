@@ -111,6 +111,14 @@ ENCODER_CASES = {
                  model=dict(num_fusion_layers=1, num_fusion_stack=1, num_graph_stack=1, bert_layers=12, vit_layers=12)),
 }
 
+# Separate fixture file (encoder_big.npz): graphs past one 128-wide attention tile, so an encoder-level check runs the
+# persistent forward (attn_fwd3_kernel), the tail-key backward and the n > 128 collate path against the reference.
+ENCODER_BIG_CASES = {
+    "big2": dict(sizes=[134, 131], seed=25, n_images=2, spmax=5,
+                 model=dict(num_fusion_layers=1, num_fusion_stack=1, num_graph_stack=2, bert_layers=3, vit_layers=3)),
+}
+ENCODER_CASES_ALL = dict(ENCODER_CASES, **ENCODER_BIG_CASES)
+
 COMMON_MODEL = dict(num_in_degree=512, num_out_degree=512, num_edges=512 * 3, num_spatial=512, num_edge_dis=128,
                     num_atoms=512 * 9, num_bottle_neck=4, embedding_dim=768, ffn_embedding_dim=768,
                     num_attention_heads=12, encoder_normalize_before=True, pre_layernorm=False,
@@ -118,6 +126,6 @@ COMMON_MODEL = dict(num_in_degree=512, num_out_degree=512, num_edges=512 * 3, nu
 
 
 def encoder_items(name, list_distance=False):
-    c = ENCODER_CASES[name]
+    c = ENCODER_CASES_ALL[name]
     kw = dict(n_images=c["n_images"]) if c["n_images"] else dict(with_images=False)
     return syn.synthetic_items(c["sizes"], c["seed"], list_distance=list_distance, **kw), c["spmax"]

@@ -1,6 +1,6 @@
 """Generate the golden fixtures by running the UNMODIFIED reference in this container.
 
-    python tests/golden/make_golden.py [--only apsp,hops,collate,modules,encoder] [--skip-cfg1]
+    python tests/golden/make_golden.py [--only apsp,hops,collate,modules,encoder,encoder_big] [--skip-cfg1]
 
 Needs ``/root/reference`` (absent on the GPU box), so the outputs are committed:
 ``tests/golden/*.npz`` / ``*.json``.  Inputs are rebuilt from the seeds in ``cases.py``.
@@ -27,10 +27,26 @@ import ref_harness as rh  # noqa: E402
 from mdt_oracle import seed_parameters  # noqa: E402  (name-keyed seeding helper only)
 
 
+# tests/test_live_reference.py sets this to a dict: fixtures are then kept in memory (name -> arrays / object)
+# instead of being written, and compared with the committed files.
+CAPTURE = None
+
+
 def save(name, **arrays):
+    if CAPTURE is not None:
+        CAPTURE[name] = {k: np.asarray(v) for k, v in arrays.items()}
+        return
     path = os.path.join(HERE, name)
     np.savez_compressed(path, **arrays)
     print(f"  wrote {name}  ({os.path.getsize(path) / 1024:.1f} KiB)")
+
+
+def save_json(name, obj, indent=1):
+    if CAPTURE is not None:
+        CAPTURE[name] = obj
+        return
+    json.dump(obj, open(os.path.join(HERE, name), "w"), indent=indent)
+    print(f"  wrote {name}")
 
 
 def gen_apsp():
@@ -57,8 +73,7 @@ def gen_apsp():
         M, path = algos.floyd_warshall(adj)
         dig[name] = {"M": cases.digest(np.asarray(M)), "path": cases.digest(np.asarray(path)),
                      "n": int(adj.shape[0]), "ref_seconds": round(time.time() - t, 4)}
-    json.dump(dig, open(os.path.join(HERE, "apsp_digests.json"), "w"), indent=1)
-    print("  wrote apsp_digests.json")
+    save_json("apsp_digests.json", dig)
 
 
 def gen_hops():
@@ -187,59 +202,80 @@ def gen_modules():
     save("graph_modules.npz", **out)
 
 
-def gen_encoder(skip_cfg1=False):
+def _encoder_case(name, c, out, meta):
+    t0 = time.time()
+    items, spmax = cases.encoder_items(name, list_distance=True)
+    batch = _ref_collate(items, spmax)
+    m = dict(c["model"])
+    bl, vl = m.pop("bert_layers"), m.pop("vit_layers")
+    with rh.reference_runtime(bert_layers=bl, vit_layers=vl) as mods:
+        kw = dict(cases.COMMON_MODEL)
+        kw.update(m)
+        enc = mods.MultiGraphormerGraphEncoder(multi_hop_max_dist=5, dropout=0.0, attention_dropout=0.0,
+                                               activation_dropout=0.0, **kw)
+        seed_parameters(enc, 41)
+        enc.eval()
+        t1 = time.time()
+        out_all, glob, loss = rh.reference_head_and_loss(enc, batch)
+        t2 = time.time()
+        loss.backward()
+        t3 = time.time()
+    out[f"{name}.out_all"] = out_all.detach().numpy()
+    out[f"{name}.global"] = glob.detach().numpy()
+    out[f"{name}.loss"] = np.array(float(loss))
+    norms = {}
+    for n_, p_ in enc.named_parameters():
+        norms[n_] = None if p_.grad is None else float(p_.grad.double().norm())
+    out[f"{name}.grad.spatial_pos_encoder"] = enc.graph_attn_bias.spatial_pos_encoder.weight.grad[:24].numpy()
+    out[f"{name}.grad.virtual_distance"] = enc.graph_attn_bias.graph_token_virtual_distance.weight.grad.numpy()
+    out[f"{name}.grad.bottle_neck"] = enc.bottle_neck.weight.grad.numpy()
+    out[f"{name}.grad.in_degree_encoder"] = enc.graph_node_feature.in_degree_encoder.weight.grad[:8].numpy()
+    out[f"{name}.grad.q_proj0"] = enc.layers[0].layers[0].self_attn.q_proj.weight.grad[:4].numpy()
+    # criterion counters of hatespeech_loss.py:102-110 on the reference logits (for the product-criterion GPU test)
+    logits = out_all.detach()[batch["y_mask"]].float()
+    targets = torch.flatten(batch["y"]).long()
+    pred = logits.argmax(-1)
+    out[f"{name}.counters"] = np.array([logits.shape[0], int((pred == targets).sum()), int(((pred == targets) & (pred == 1)).sum()),
+                                        int((targets == 1).sum()), int((pred == 1).sum())], dtype=np.int64)
+    f0 = enc.fusion_layers[0].fusion_layers[0].bert_encoder
+    out[f"{name}.grad.fusion0_query"] = f0.attention.self.query.weight.grad[:4].numpy()
+    out[f"{name}.grad.fusion0_inter"] = f0.intermediate.dense.weight.grad[:4].numpy()
+    out[f"{name}.grad.classifier"] = enc.node_classifier.weight.grad.numpy()
+    meta[name] = dict(grad_norms=norms, n_params=sum(p.numel() for p in enc.parameters()),
+                      ref_fwd_s=round(t2 - t1, 3), ref_bwd_s=round(t3 - t2, 3), build_s=round(t1 - t0, 3),
+                      state_keys=len(enc.state_dict()))
+    print(f"  encoder case {name}: loss={float(loss):.6f} fwd={t2 - t1:.2f}s bwd={t3 - t2:.2f}s")
+
+
+def gen_encoder_big():
+    meta, out = {}, {}
+    for name, c in cases.ENCODER_BIG_CASES.items():
+        _encoder_case(name, c, out, meta)
+    save("encoder_big.npz", **out)
+    save_json("encoder_big_meta.json", meta)
+
+
+def gen_encoder(skip_cfg1=False, only=None):
     meta = {}
     out = {}
     for name, c in cases.ENCODER_CASES.items():
-        if name == "cfg1" and skip_cfg1:
+        if (name == "cfg1" and skip_cfg1) or (only is not None and name not in only):
             continue
-        t0 = time.time()
-        items, spmax = cases.encoder_items(name, list_distance=True)
-        batch = _ref_collate(items, spmax)
-        m = dict(c["model"])
-        bl, vl = m.pop("bert_layers"), m.pop("vit_layers")
-        with rh.reference_runtime(bert_layers=bl, vit_layers=vl) as mods:
-            kw = dict(cases.COMMON_MODEL)
-            kw.update(m)
-            enc = mods.MultiGraphormerGraphEncoder(multi_hop_max_dist=5, dropout=0.0, attention_dropout=0.0,
-                                                   activation_dropout=0.0, **kw)
-            seed_parameters(enc, 41)
-            enc.eval()
-            t1 = time.time()
-            out_all, glob, loss = rh.reference_head_and_loss(enc, batch)
-            t2 = time.time()
-            loss.backward()
-            t3 = time.time()
-        out[f"{name}.out_all"] = out_all.detach().numpy()
-        out[f"{name}.global"] = glob.detach().numpy()
-        out[f"{name}.loss"] = np.array(float(loss))
-        norms = {}
-        for n_, p_ in enc.named_parameters():
-            norms[n_] = None if p_.grad is None else float(p_.grad.double().norm())
-        out[f"{name}.grad.spatial_pos_encoder"] = enc.graph_attn_bias.spatial_pos_encoder.weight.grad[:24].numpy()
-        out[f"{name}.grad.virtual_distance"] = enc.graph_attn_bias.graph_token_virtual_distance.weight.grad.numpy()
-        out[f"{name}.grad.bottle_neck"] = enc.bottle_neck.weight.grad.numpy()
-        out[f"{name}.grad.in_degree_encoder"] = enc.graph_node_feature.in_degree_encoder.weight.grad[:8].numpy()
-        out[f"{name}.grad.q_proj0"] = enc.layers[0].layers[0].self_attn.q_proj.weight.grad[:4].numpy()
-        meta[name] = dict(grad_norms=norms, n_params=sum(p.numel() for p in enc.parameters()),
-                          ref_fwd_s=round(t2 - t1, 3), ref_bwd_s=round(t3 - t2, 3), build_s=round(t1 - t0, 3),
-                          state_keys=len(enc.state_dict()))
-        print(f"  encoder case {name}: loss={float(loss):.6f} fwd={t2 - t1:.2f}s bwd={t3 - t2:.2f}s")
+        _encoder_case(name, c, out, meta)
     save("encoder.npz", **out)
-    json.dump(meta, open(os.path.join(HERE, "encoder_meta.json"), "w"), indent=1)
+    save_json("encoder_meta.json", meta)
     # reference state-dict key list (drop-in checkpoint compatibility test)
     with rh.reference_runtime(bert_layers=3, vit_layers=3) as mods:
         kw = dict(cases.COMMON_MODEL)
         kw.update(num_fusion_layers=1, num_fusion_stack=1, num_graph_stack=1)
         enc = mods.MultiGraphormerGraphEncoder(multi_hop_max_dist=5, **kw)
         keys = {k: list(v.shape) for k, v in enc.state_dict().items()}
-    json.dump(keys, open(os.path.join(HERE, "encoder_state_keys.json"), "w"), indent=0)
-    print("  wrote encoder_meta.json, encoder_state_keys.json")
+    save_json("encoder_state_keys.json", keys, indent=0)
 
 
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
-    ap.add_argument("--only", default="apsp,hops,collate,modules,encoder")
+    ap.add_argument("--only", default="apsp,hops,collate,modules,encoder,encoder_big")
     ap.add_argument("--skip-cfg1", action="store_true")
     a = ap.parse_args()
     assert rh.reference_available(), "needs /root/reference"
@@ -248,4 +284,4 @@ if __name__ == "__main__":
     for part in a.only.split(","):
         print(f"[{part}]")
         {"apsp": gen_apsp, "hops": gen_hops, "collate": gen_collate, "modules": gen_modules,
-         "encoder": lambda: gen_encoder(a.skip_cfg1)}[part]()
+         "encoder": lambda: gen_encoder(a.skip_cfg1), "encoder_big": gen_encoder_big}[part]()

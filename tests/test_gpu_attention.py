@@ -210,7 +210,7 @@ def run_backward(ops, q, k, v, bias=None, code=None, lut=None, key_pad=None, see
     return got, want
 
 
-@pytest.mark.parametrize("T", [1, 7, 64, 65, 128, 129, 200, 257, 513])
+@pytest.mark.parametrize("T", [1, 7, 64, 65, 128, 129, 130, 136, 200, 257, 264, 513])
 @pytest.mark.parametrize("mode", ["none", "f32", "bf16", "code"])
 def test_backward_modes(ops, T, mode):
     B, H = (2, 2) if T > 300 else (3, 4)
@@ -245,6 +245,35 @@ def test_backward_strided_layouts_and_key_padding(ops, layout):
     pad = kp[:, :, None, None].expand_as(got["dk"])
     assert float(got["dk"].float()[pad].abs().max()) == 0.0
     assert float(got["dv"].float()[pad].abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("T", [100, 129, 300])
+def test_wide_spatial_codes_forward_and_gradient_contract(ops, T):
+    """include/mdt_b200.h: spatial codes 0..61 are legal in every kernel (the persistent forward indexes 64 entries);
+    grad_lut is exact for codes 0..22 and 254, gradients of codes 23..61 are accumulated into entry 22."""
+    B, H = 2, 4
+    q, k, v = make_qkv(B, T, H, seed=300 + T)
+    g = torch.Generator().manual_seed(T)
+    pitch = (T + 15) // 16 * 16
+    code = torch.randint(0, 62, (B, T, pitch), generator=g, dtype=torch.int64)
+    code[:, 0, :] = 254
+    code[:, :, 0] = 254
+    mask = torch.rand(B, T, pitch, generator=g) < 0.3
+    idx = torch.arange(T)
+    mask[:, idx, idx] = False
+    code[mask] = 255
+    code = code.to(torch.uint8).cuda()
+    lut = (torch.randn(H, 256, generator=g) * 0.5).cuda()
+    o = ops.biased_attention(q, k, v, code=code, lut=lut)
+    o_ref = reference(q, k, v, code_to_bias(code, lut, T))
+    assert float((o.float() - o_ref).abs().max()) <= FWD_ATOL
+    got, want = run_backward(ops, q, k, v, code=code, lut=lut, seed=T)
+    for name in ("dq", "dk", "dv"):
+        assert rel_err(got[name], want[name]) <= GRAD_RTOL, name
+    folded = want["dlut"].clone()
+    folded[:, 22] = want["dlut"][:, 22:62].sum(1)
+    folded[:, 23:62] = 0
+    assert rel_err(got["dlut"], folded) <= GRAD_RTOL
 
 
 def test_backward_T1025(ops):

@@ -176,3 +176,31 @@ def test_prepend_tokens_equals_cat_with_gradients():
     go = torch.randn(ref.shape, generator=g)
     for a, b in zip(torch.autograd.grad(got, (bn, full), go), torch.autograd.grad(ref, (bn, full), go)):
         assert torch.equal(a, b)
+
+
+def test_check_discussion_tree_refuses_non_trees():
+    """the device path re-derives hop pairs from a tree rooted at node 0; everything else must raise."""
+    from multimodaldiscussiontransformer_b200.data import synthetic as syn
+    from multimodaldiscussiontransformer_b200.data.collator import HostBatch, check_discussion_tree
+
+    items = syn.synthetic_items([6, 4, 1], 3, with_images=False)
+    HostBatch(items, pin=False)                                 # trees (and a lone post) pass
+    e = np.asarray(items[0].edge_index).copy()                  # [parent->child x5 | child->parent x5]
+    check_discussion_tree(e, 6)
+    with pytest.raises(ValueError):                             # a cycle: one edge too many
+        check_discussion_tree(np.concatenate([e, np.array([[1, 5], [5, 1]])], axis=1), 6)
+    with pytest.raises(ValueError):                             # a forest: one reply edge missing
+        check_discussion_tree(np.delete(e, [4, 9], axis=1), 6)
+    with pytest.raises(ValueError):                             # one direction listed twice, the other never
+        check_discussion_tree(np.concatenate([e[:, :5], e[:, :5]], axis=1), 6)
+    bad = e.copy()
+    bad[0, 0] = 7
+    with pytest.raises(ValueError):                             # endpoint outside the graph
+        check_discussion_tree(bad, 6)
+    # right edge count, symmetric, but a cycle plus a disconnected node
+    cyc = np.array([[0, 1, 2, 0, 1, 2, 3, 4], [1, 2, 0, 2, 0, 1, 4, 3]])
+    with pytest.raises(ValueError):
+        check_discussion_tree(cyc, 5)
+    items[1].edge_index = np.delete(np.asarray(items[1].edge_index), [2, 5], axis=1)
+    with pytest.raises(ValueError):
+        HostBatch(items, pin=False)
