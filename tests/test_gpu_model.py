@@ -7,10 +7,12 @@ by the UNMODIFIED reference (tests/golden/make_golden.py), at sizes that reach t
   tail-key backward and the n > 128 collate path run under an encoder-level check;
 * the ``tiny*`` cases through ``GraphormerModel.build_model`` + ``GraphPredictionNodeCrossEntropy``.
 
-Tolerances (bf16 kernels vs the reference's fp32 CPU run): fp32 parameters -- logits <= 2e-2 abs, loss
-<= 2 %, sampled gradients <= 5e-2 relative Frobenius; bf16 parameters (what the bench runs) -- logits
-<= 6e-2 abs, loss <= 4 %, sampled gradients <= 1.5e-1 relative Frobenius (bf16 weights carry 3 significant
-digits through up to 12 transformer layers)."""
+Tolerances (bf16 kernels vs the reference's fp32 CPU run), with the worst value measured on a B200 over all
+cases (profiles/parity_r02/*.json) in brackets: fp32 parameters -- logits <= 5e-3 abs [3e-4], graph embedding
+<= 1e-2 [3.5e-3], loss <= 0.5 % [0.01 %], sampled gradients <= 3e-2 relative Frobenius [1.5e-2]; bf16 parameters
+(what the bench runs, padded or packed text) -- logits <= 2e-2 abs [7.7e-3], graph embedding <= 6e-2 [4.5e-2],
+loss <= 1 % [0.2 %], sampled gradients <= 1.2e-1 relative Frobenius [9.8e-2, q_proj rows of a 4-graph-layer
+case; <= 4e-2 elsewhere]: bf16 weights carry 3 significant digits through up to 12 transformer layers."""
 
 from __future__ import annotations
 
@@ -34,9 +36,9 @@ import cases  # noqa: E402
 import mdt_oracle as orc  # noqa: E402  (checker / name-keyed parameter seeding only)
 
 TOL = {  # mode -> (logits abs, loss rel, grads rel Frobenius, global abs)
-    "fp32": (2e-2, 2e-2, 5e-2, 5e-2),
-    "bf16": (6e-2, 4e-2, 1.5e-1, 1.5e-1),
-    "bf16_packed": (6e-2, 4e-2, 1.5e-1, 1.5e-1),
+    "fp32": (5e-3, 5e-3, 3e-2, 1e-2),
+    "bf16": (2e-2, 1e-2, 1.2e-1, 6e-2),
+    "bf16_packed": (2e-2, 1e-2, 1.2e-1, 6e-2),
 }
 
 
@@ -113,7 +115,7 @@ def run_case(name, mode):
     measured = {
         "logits_max_abs": float((logits.float().cpu() - want).abs().max()),
         "global_max_abs": float((glob.float().cpu() - torch.from_numpy(gold[f"{name}.global"])).abs().max()),
-        "loss": float(loss), "ref_loss": ref_loss,
+        "loss": float(loss.detach()), "ref_loss": ref_loss,
         "grads_rel": {k: (rel(g, r) if g is not None else None) for k, (g, r) in checks.items()},
     }
     out_dir = os.path.join(HERE, "..", "gpurun_out")
