@@ -46,6 +46,7 @@ def main():
     ap.add_argument("--n", type=int, default=4096)
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--json", default=None)
+    ap.add_argument("--skip-padded", action="store_true")
     ap.add_argument("--jagged", action="store_true",
                     help="also try cuDNN SDPA on jagged nested tensors (on torch 2.11 this call went into an fx trace of the "
                          "nested-tensor ops and did not return within 5 minutes on the B200 box)")
@@ -79,6 +80,24 @@ def main():
     from flash_attn import flash_attn_varlen_func
     ref = run("flash_varlen", lambda: flash_attn_varlen_func(q, k, v, cu_d, cu_d, Tmax, Tmax), (q, k, v), go)
 
+    # this repo's packed-sequence kernels (csrc/attn_varlen.cu): grouped tiles and one sequence per tile
+    from multimodaldiscussiontransformer_b200 import ops as mops
+    qkv = torch.stack([q.detach(), k.detach(), v.detach()], dim=1).contiguous().requires_grad_(True)
+    bytes_fwd = 4.0 * total * H * d * 2            # q, k, v in, o out
+    bytes_bwd = 8.0 * total * H * d * 2            # q, k, v, o, do in; dq, dk, dv out
+    for group in (True, False):
+        plan = mops.varlen_plan(cu_d, group=group)
+        name = "mdt_varlen" if group else "mdt_varlen_ungrouped"
+        o = run(name, lambda: mops.varlen_attention(qkv, cu_d, plan), (qkv,), go)
+        if o is not None:
+            c = out["cases"][name]
+            c["n_items"] = int(plan[0])
+            c["fwd_hbm_gbs"] = bytes_fwd / c["fwd_us"] / 1e3
+            c["bwd_hbm_gbs"] = bytes_bwd / c["bwd_us"] / 1e3
+            if ref is not None:
+                c["max_abs_diff_vs_flash"] = float((o.float() - ref.float()).abs().max())
+            print(name, json.dumps(c), flush=True)
+
     from torch.nn.attention import SDPBackend, sdpa_kernel
 
     def jag(t):
@@ -93,6 +112,11 @@ def main():
         if o is not None and ref is not None:
             out["cases"]["cudnn_jagged"]["max_abs_diff_vs_flash"] = float((o.float() - ref.float()).abs().max())
 
+    if a.skip_padded:
+        print(json.dumps(out))
+        if a.json:
+            json.dump(out, open(a.json, "w"), indent=1)
+        return
     # padded layouts
     T = Tmax
     idx = torch.arange(T, device="cuda")[None, :] < lens.cuda()[:, None]          # [n, T] valid

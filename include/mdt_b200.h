@@ -165,6 +165,35 @@ int mdt_biased_attn_bwd(const void *q, const void *k, const void *v, const void 
                         mdt_stream_t stream);
 
 /* ------------------------------------------------------------------------------------
+ * N1  self-attention over PACKED (unpadded) sequences: the BERT side of the fusion layers
+ *     mDT/src/modules/multi_graphormer_fusion_layer.py:105-149 (Hugging Face BertSelfAttention called at :138-148:
+ *     softmax(q k^T / sqrt(d) + key mask) v with dropout on the probabilities), mDT/src/modules/multigraphormer_graph_encoder.py:341-362
+ *   Tokens of all comments are laid end to end: sequence s = rows [cu_seqlens[s], cu_seqlens[s+1]) of q / k / v
+ *   (bf16, row r / head h / channel c at r*stride + h*64 + c -- e.g. the three slices of one [total,3,H,64]
+ *   projection); scores are q k^T * softmax_scale (the scale is folded into the exponent: q is NOT pre-scaled).
+ *   Every sequence must be <= 128 rows.  A padded token never influences
+ *   a real one in the reference (additive key mask), so attention restricted to each sequence is the same function.
+ *   mdt_varlen_attn_plan groups consecutive sequences into <= 128-row tiles (group != 0; group == 0: one sequence
+ *   per tile): plan int32 [n_seq + 3] = {n_items, error flag (a sequence > 128 rows: the attention calls then do
+ *   nothing), first sequence of item 0, ..., n_seq}.  Build it once per batch; every layer, forward and backward, reuses it.
+ *   forward : out [total, H*64] (row stride o_stride), lse f32 [H, total]
+ *   backward: dq / dk / dv rows like q / k / v with their own strides (each row written exactly once: no atomics,
+ *             no scratch); out / grad_out rows with o_stride / g_stride.
+ *   Dropout (BertSelfAttention.dropout) is a counter hash of (seed, item, head, row, column) regenerated in the
+ *   backward, so forward and backward must be given the same plan.
+ * ------------------------------------------------------------------------------------ */
+int mdt_varlen_attn_plan(const int32_t *cu_seqlens, int n_seq, int group, int32_t *plan, mdt_stream_t stream);
+int mdt_varlen_attn_fwd(const void *q, const void *k, const void *v, int64_t q_stride, int64_t k_stride, int64_t v_stride,
+                        int total, int H, const int32_t *cu_seqlens, int n_seq, const int32_t *plan, void *out,
+                        int64_t o_stride, float *lse, float softmax_scale, float dropout_p, uint64_t dropout_seed,
+                        mdt_stream_t stream);
+int mdt_varlen_attn_bwd(const void *q, const void *k, const void *v, int64_t q_stride, int64_t k_stride, int64_t v_stride,
+                        const void *out, int64_t o_stride, const void *grad_out, int64_t g_stride, const float *lse,
+                        int total, int H, const int32_t *cu_seqlens, int n_seq, const int32_t *plan, void *dq, void *dk,
+                        void *dv, int64_t dq_stride, int64_t dk_stride, int64_t dv_stride, float softmax_scale,
+                        float dropout_p, uint64_t dropout_seed, mdt_stream_t stream);
+
+/* ------------------------------------------------------------------------------------
  * A4  GraphNodeFeature.forward               mDT/src/modules/graphormer_layers.py:39-50
  *   out[b,0,:] = graph_token; out[b,1+i,:] = x[b,i,:] + E_in[in_degree[b,i]] + E_out[out_degree[b,i]]
  *   x [B,N,C], tables [num_degree,C], out [B,N+1,C], all `dtype`; degrees int64.

@@ -6,6 +6,7 @@ when ``x_image_indexes`` is given as an int row list."""
 
 from __future__ import annotations
 
+import os
 from typing import Optional
 
 import torch
@@ -49,6 +50,7 @@ class TextPack:
         cu = torch.zeros(n + 1, dtype=torch.int64, device=dev)
         cu[1:] = torch.cumsum(lens + nb, 0)
         self.cu_seqlens = cu.to(torch.int32)
+        self._plan = None
         seq = torch.repeat_interleave(torch.arange(n, device=dev), lens, output_size=text_tokens)
         cu_text = torch.cumsum(lens, 0) - lens
         pos = torch.arange(text_tokens, device=dev) - cu_text[seq]
@@ -59,6 +61,13 @@ class TextPack:
         cu0 = torch.zeros(n + 1, dtype=torch.int64, device=dev)
         cu0[1:] = torch.cumsum(lens, 0)
         self.text_only = _SeqLens(cu0.to(torch.int32), text_max)
+
+    @property
+    def plan(self):
+        """Tile plan of the packed attention kernel (csrc/attn_varlen.cu): built once, shared by all layers and passes."""
+        if self._plan is None:
+            self._plan = ops.varlen_plan(self.cu_seqlens)
+        return self._plan
 
     def gather_text(self, text_padded: torch.Tensor) -> torch.Tensor:
         """padded ``[n, L, C]`` -> the real tokens ``[text_tokens, C]`` in sequence order (layout of ``text_only``)."""
@@ -80,14 +89,28 @@ class TextPack:
 class _SeqLens:
     def __init__(self, cu_seqlens, max_seqlen):
         self.cu_seqlens, self.max_seqlen = cu_seqlens, max_seqlen
+        self._plan = None
+
+    @property
+    def plan(self):
+        if self._plan is None:
+            self._plan = ops.varlen_plan(self.cu_seqlens)
+        return self._plan
 
 
+#: "mdt" = this library's tcgen05 kernels (csrc/attn_varlen.cu); "flash" = flash-attn's varlen entry, kept only as the
+#: A/B comparison of benchmarks/text_attn_probe.py (MDT_TEXT_ATTN=flash) -- never a fallback: "mdt" raises when it cannot run.
+TEXT_ATTN_IMPL = os.environ.get("MDT_TEXT_ATTN", "mdt")
 _FLASH = None
 
 
 def _varlen_attention(qkv, pack, dropout_p: float):
-    """Self-attention over the packed sequences: ``[total, 3, H, d]`` -> ``[total, H, d]`` (library kernel: flash-attn;
-    the packed-QKV entry point returns one ``[total, 3, H, d]`` gradient, so autograd never re-assembles three slices)."""
+    """Self-attention over the packed sequences: ``[total, 3, H, 64]`` -> ``[total, H, 64]``; one ``[total, 3, H, 64]``
+    gradient comes back, so autograd never re-assembles three slices."""
+    if TEXT_ATTN_IMPL == "mdt":
+        if pack.max_seqlen > 128:
+            raise RuntimeError(f"packed text attention handles sequences of <= 128 rows, got {pack.max_seqlen}")
+        return ops.varlen_attention(qkv, pack.cu_seqlens, pack.plan, dropout_p=dropout_p)
     global _FLASH
     if _FLASH is None:
         from flash_attn import flash_attn_varlen_qkvpacked_func

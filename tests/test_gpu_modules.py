@@ -174,7 +174,6 @@ def test_reference_format_batch_matches_fast_path():
 def test_packed_text_fusion_matches_padded_path(name):
     """the BERT side of the fusion layers on packed (unpadded) tokens gives the same logits, bottleneck
     tokens, graph embedding, real-token hidden states and gradients as the padded Hugging Face path (bf16 model)."""
-    pytest.importorskip("flash_attn")
     from multimodaldiscussiontransformer_b200.data.collator import collator
 
     enc = build_encoder(name).to(torch.bfloat16)
