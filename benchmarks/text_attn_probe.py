@@ -86,12 +86,12 @@ def main():
     bytes_fwd = 4.0 * total * H * d * 2            # q, k, v in, o out
     bytes_bwd = 8.0 * total * H * d * 2            # q, k, v, o, do in; dq, dk, dv out
     for group in (True, False):
-        plan = mops.varlen_plan(cu_d, group=group)
+        plan = mops.varlen_plan(cu_d, total, group=group)
         name = "mdt_varlen" if group else "mdt_varlen_ungrouped"
-        o = run(name, lambda: mops.varlen_attention(qkv, cu_d, plan), (qkv,), go)
+        o = run(name, lambda: mops.varlen_attention(qkv, plan), (qkv,), go)
         if o is not None:
             c = out["cases"][name]
-            c["n_items"] = int(plan[0])
+            c["n_items"] = plan.n_items()
             c["fwd_hbm_gbs"] = bytes_fwd / c["fwd_us"] / 1e3
             c["bwd_hbm_gbs"] = bytes_bwd / c["bwd_us"] / 1e3
             if ref is not None:

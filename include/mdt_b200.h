@@ -174,24 +174,27 @@ int mdt_biased_attn_bwd(const void *q, const void *k, const void *v, const void 
  *   Every sequence must be <= 128 rows.  A padded token never influences
  *   a real one in the reference (additive key mask), so attention restricted to each sequence is the same function.
  *   mdt_varlen_attn_plan groups consecutive sequences into <= 128-row tiles (group != 0; group == 0: one sequence
- *   per tile): plan int32 [n_seq + 3] = {n_items, error flag (a sequence > 128 rows: the attention calls then do
- *   nothing), first sequence of item 0, ..., n_seq}.  Build it once per batch; every layer, forward and backward, reuses it.
+ *   per tile) and precomputes every packed row's key window.  plan is int32 [mdt_varlen_attn_plan_words(n_seq, total)]:
+ *     [0] n_items  [1] error flag (a sequence > 128 rows: the attention calls then do nothing)  [2] n_seq  [3] total
+ *     [4 + 2i] first row of item i, [5 + 2i] its first sequence (i = 0..n_items; entry n_items = {total, n_seq})
+ *     then n_seq scratch words and `total` row windows (lo | hi << 16, relative to the item's first row).
+ *   Build it once per batch; every layer, forward and backward, reuses it (cu_seqlens is not read again).
  *   forward : out [total, H*64] (row stride o_stride), lse f32 [H, total]
  *   backward: dq / dk / dv rows like q / k / v with their own strides (each row written exactly once: no atomics,
  *             no scratch); out / grad_out rows with o_stride / g_stride.
  *   Dropout (BertSelfAttention.dropout) is a counter hash of (seed, item, head, row, column) regenerated in the
  *   backward, so forward and backward must be given the same plan.
  * ------------------------------------------------------------------------------------ */
-int mdt_varlen_attn_plan(const int32_t *cu_seqlens, int n_seq, int group, int32_t *plan, mdt_stream_t stream);
+int64_t mdt_varlen_attn_plan_words(int n_seq, int total);
+int mdt_varlen_attn_plan(const int32_t *cu_seqlens, int n_seq, int total, int group, int32_t *plan, mdt_stream_t stream);
 int mdt_varlen_attn_fwd(const void *q, const void *k, const void *v, int64_t q_stride, int64_t k_stride, int64_t v_stride,
-                        int total, int H, const int32_t *cu_seqlens, int n_seq, const int32_t *plan, void *out,
-                        int64_t o_stride, float *lse, float softmax_scale, float dropout_p, uint64_t dropout_seed,
-                        mdt_stream_t stream);
+                        int total, int H, int n_seq, const int32_t *plan, void *out, int64_t o_stride, float *lse,
+                        float softmax_scale, float dropout_p, uint64_t dropout_seed, mdt_stream_t stream);
 int mdt_varlen_attn_bwd(const void *q, const void *k, const void *v, int64_t q_stride, int64_t k_stride, int64_t v_stride,
                         const void *out, int64_t o_stride, const void *grad_out, int64_t g_stride, const float *lse,
-                        int total, int H, const int32_t *cu_seqlens, int n_seq, const int32_t *plan, void *dq, void *dk,
-                        void *dv, int64_t dq_stride, int64_t dk_stride, int64_t dv_stride, float softmax_scale,
-                        float dropout_p, uint64_t dropout_seed, mdt_stream_t stream);
+                        int total, int H, int n_seq, const int32_t *plan, void *dq, void *dk, void *dv,
+                        int64_t dq_stride, int64_t dk_stride, int64_t dv_stride, float softmax_scale, float dropout_p,
+                        uint64_t dropout_seed, mdt_stream_t stream);
 
 /* ------------------------------------------------------------------------------------
  * A4  GraphNodeFeature.forward               mDT/src/modules/graphormer_layers.py:39-50

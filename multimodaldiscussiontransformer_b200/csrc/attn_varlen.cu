@@ -7,16 +7,23 @@
 // A work unit is (item, head).  An ITEM is a run of consecutive sequences that fits one 128-row tile (built once per batch
 // by mdt_varlen_attn_plan and shared by all layers, forward and backward): the tile is loaded with ONE TMA box per operand
 // (2-D map over [total, row_stride], 128-byte swizzle), S = Q K^T is one 128x128x64 tcgen05.mma, and attention stays
-// inside each sequence through a per-row column window [lo, hi) -- the block-diagonal mask.  Short comments (mean 62 rows)
-// would otherwise leave half of every tile, and half of every TMEM lane quarter's threads, idle.
+// inside each sequence through a per-row column window [lo, hi) -- the block-diagonal mask, precomputed per packed row by
+// the plan kernel.  Short comments (mean 62 rows) would otherwise leave half of every tile, and half of every TMEM lane
+// quarter's threads, idle.
 //
-// forward   S = Q K^T -> TMEM; thread r = query row r (TMEM lane r): two passes over the 32-column chunks that hold live
-//           keys (row maximum; p = 2^(x - m), row sum, dropout, bf16 P tile in shared memory); O = P V (k-steps only over
-//           the live key chunks); O / l -> out, lse.  2 CTAs / SM; the next unit's Q, K (after S) and V (after P V) are
-//           prefetched under the current unit's softmax / epilogue.
-// backward  S = Q K^T, dP = dO V^T -> TMEM; delta = rowsum(dO * O) from global under the TMA latency; P = 2^(S - lse),
+// 256 threads per CTA, 2 CTAs per SM: threads r and r + 128 share query row r (= TMEM lane r) and split its key columns
+// ([0,64) / [64,128)) and its 64 output columns, so a unit's softmax / epilogue latency is half of the one-thread-per-row
+// form and 16 warps per SM hide the TMEM / shared-memory / MUFU latencies.
+//
+// forward   S = Q K^T -> TMEM; each thread holds its <= 64 scores in registers: masking only in the 32-column chunks the
+//           row's window cuts through, zero stores in chunks of other sequences; the halves exchange row maximum and row
+//           sum through shared memory; bf16 P tile -> O = P V (k-steps over live key chunks only); O / l -> out, lse.
+//           The next unit's Q, K (after S) and V (after P V) are prefetched under the current unit's softmax / epilogue.
+// backward  S = Q K^T, dP = dO V^T -> TMEM; delta = rowsum(dO * O) = rowsum(keep P dP / (1 - p)) from the two accumulators
+//           (no O / dO rows from global memory); P = 2^(S - lse),
 //           dS = P * (keep * dP / (1 - p) - delta) -> bf16 tiles [query][key]; dV = P^T dO, dK = dS^T Q (A read MN-major),
 //           dQ = dS K.  No atomics, no dq scratch: a tile holds whole sequences, so each gradient row is written once.
+//           The next unit's four tiles are requested as soon as the last MMAs have completed, under the epilogue.
 #include <initializer_list>
 
 #include "attn_common.cuh"
@@ -25,13 +32,19 @@ namespace mdt {
 namespace attn {
 using namespace sm100;
 
-constexpr int kVlThreads = 128;
+constexpr int kVlThreads = 256;
+
+// plan layout (int32): [0] n_items  [1] error flag  [2] n_seq  [3] total
+//   [4 + 2 i] first row of item i, [5 + 2 i] its first sequence, i = 0 .. n_items (entry n_items = {total, n_seq})
+//   then n_seq words of scratch, then `total` row windows: lo | hi << 16, relative to the item's first row
+__host__ __device__ constexpr int plan_items_off() { return 4; }
+__host__ __device__ inline int plan_scratch_off(int n_seq) { return 4 + 2 * (n_seq + 1); }
+__host__ __device__ inline int plan_rows_off(int n_seq) { return plan_scratch_off(n_seq) + n_seq; }
 
 struct VarlenArgs {
-    int total, H;
-    const int32_t *cu;    // [n_seq + 1]
-    const int32_t *plan;  // [0] = n_items, [1] = error flag, [2 + i] = first sequence of item i, [2 + n_items] = n_seq
-    __nv_bfloat16 *out;   // forward: O rows; backward: unused
+    int total, H, n_seq;
+    const int32_t *plan;
+    __nv_bfloat16 *out;   // forward: O rows
     int64_t o_stride;
     float *lse;           // [H, total]
     float scale, scale_log2;  // softmax scale (> 0) and scale * log2(e): scores are scaled inside the exponent
@@ -53,64 +66,67 @@ __device__ __forceinline__ uint32_t window_bits(int lo, int hi, int c) {
 }
 
 struct VlUnit {
-    int row0, nrows, lo, hi, h;
-    bool valid;
+    int row0, nrows, h;
 };
-// item / head of work unit w and this thread's row window
-__device__ __forceinline__ VlUnit vl_unit(const VarlenArgs &a, int w, int r) {
+__device__ __forceinline__ VlUnit vl_unit(const VarlenArgs &a, int w) {
     VlUnit u;
     const int item = w / a.H;
     u.h = w - item * a.H;
-    const int s0 = a.plan[2 + item], s1 = a.plan[3 + item];
-    u.row0 = __ldg(a.cu + s0);
-    u.nrows = min(__ldg(a.cu + s1) - u.row0, 128);
-    u.valid = r < u.nrows;
-    u.lo = u.hi = 0;
-    if (u.valid) {
-        const int g = u.row0 + r;
-        int start = u.row0;
-        for (int s = s0; s < s1; ++s) {
-            const int end = __ldg(a.cu + s + 1);
-            if (g < end) {
-                u.lo = start - u.row0;
-                u.hi = end - u.row0;
-                break;
-            }
-            start = end;
-        }
-    }
+    const int row0 = __ldg(a.plan + plan_items_off() + 2 * item);
+    const int next_row0 = __ldg(a.plan + plan_items_off() + 2 * (item + 1));
+    u.row0 = row0;
+    u.nrows = min(next_row0 - row0, 128);
     return u;
 }
 
 // ------------------------------------------------------------------------------------------------ plan
-// Greedy grouping of consecutive sequences into <= 128-row items.  One thread: the loop-carried state is a register, the
-// cu loads do not depend on it, and the plan is built once per batch (shared by every layer, forward and backward).
-__global__ void varlen_plan_kernel(const int32_t *__restrict__ cu, int n_seq, int group, int32_t *__restrict__ plan) {
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    int n_items = 0, err = 0;
-    int start_row = cu[0], s_first = 0;
-    for (int s = 0; s < n_seq; ++s) {
-        const int end = cu[s + 1];
-        if (end - cu[s] > 128) err = 1;  // a sequence longer than one tile: not this kernel's case
-        if (s > s_first && (!group || end - start_row > 128)) {  // sequence s does not fit any more: close the item before it
-            plan[2 + n_items++] = s_first;
-            s_first = s;
-            start_row = cu[s];
+// Greedy grouping of consecutive sequences into <= 128-row items by thread 0 (the loop-carried state is a register and the
+// cu loads do not depend on it), then all threads fill the per-row windows.  Built once per batch.
+__global__ void __launch_bounds__(1024) varlen_plan_kernel(const int32_t *__restrict__ cu, int n_seq, int group, int32_t *__restrict__ plan) {
+    int32_t *items = plan + plan_items_off();
+    int32_t *seq_row0 = plan + plan_scratch_off(n_seq);
+    int32_t *rowwin = plan + plan_rows_off(n_seq);
+    if (threadIdx.x == 0) {
+        int n_items = 0, err = 0;
+        int start_row = cu[0], s_first = 0;
+        for (int s = 0; s < n_seq; ++s) {
+            const int end = cu[s + 1];
+            if (end - cu[s] > 128) err = 1;  // a sequence longer than one tile: not this kernel's case
+            if (s > s_first && (!group || end - start_row > 128)) {  // sequence s does not fit any more: close the item before it
+                items[2 * n_items] = start_row;
+                items[2 * n_items + 1] = s_first;
+                ++n_items;
+                s_first = s;
+                start_row = cu[s];
+            }
+            seq_row0[s] = start_row;
         }
+        items[2 * n_items] = start_row;
+        items[2 * n_items + 1] = s_first;
+        ++n_items;
+        items[2 * n_items] = cu[n_seq];
+        items[2 * n_items + 1] = n_seq;
+        plan[0] = n_items;
+        plan[1] = err;
+        plan[2] = n_seq;
+        plan[3] = cu[n_seq];
     }
-    if (n_seq > 0) plan[2 + n_items++] = s_first;
-    plan[2 + n_items] = n_seq;
-    plan[0] = n_items;
-    plan[1] = err;
+    __syncthreads();
+    for (int s = threadIdx.x; s < n_seq; s += blockDim.x) {
+        const int a = cu[s], b = cu[s + 1], r0 = seq_row0[s];
+        const int32_t win = (a - r0) | ((b - r0) << 16);
+        for (int g = a; g < b; ++g) rowwin[g] = win;
+    }
 }
 
 // ------------------------------------------------------------------------------------------------ forward
 struct VlFwdCtrl {
     uint64_t bar_qk, bar_v, bar_s, bar_o;
     uint32_t tmem_base;
+    float xmax[2][128], xsum[2][128];
 };
 constexpr int kVlFwdTiles = 3 * 16384 + 32768;  // Q K V | P
-constexpr int kVlFwdSmem = kVlFwdTiles + 64;
+constexpr int kVlFwdSmem = kVlFwdTiles + (int)sizeof(VlFwdCtrl);
 
 __global__ void __launch_bounds__(kVlThreads, 2)
     attn_varlen_fwd_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__ CUtensorMap mk,
@@ -119,8 +135,10 @@ __global__ void __launch_bounds__(kVlThreads, 2)
     uint8_t *sQ = smem, *sK = smem + 16384, *sV = smem + 32768, *sP = smem + 49152;
     VlFwdCtrl &ctl = *reinterpret_cast<VlFwdCtrl *>(smem + kVlFwdTiles);
     const int tid = threadIdx.x, warp = tid >> 5;
+    const int r = tid & 127, hf = tid >> 7;  // query row, which half of its key / output columns
     const int n_items = a.plan[0];
     const int n_units = a.plan[1] ? 0 : n_items * a.H;  // a flagged plan (sequence > 128 rows) runs nothing
+    const int32_t *rowwin = a.plan + plan_rows_off(a.n_seq);
 
     if (tid == 0) {
         if (smem_u32(smem) & 1023u) __trap();
@@ -141,36 +159,34 @@ __global__ void __launch_bounds__(kVlThreads, 2)
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = ctl.tmem_base;
-    const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
+    const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
     const uint32_t idesc_s = idesc_bf16(128, 128, 0, 0);
     const uint32_t idesc_o = idesc_bf16(128, 64, 0, 1);
 
-    auto load_qk = [&](int w) {  // tid 0
-        const int item = w / a.H, h = w - item * a.H;
-        const int row0 = __ldg(a.cu + a.plan[2 + item]);
-        mbar_expect_tx(&ctl.bar_qk, 32768);
-        tma_load_2d(sQ, &mq, &ctl.bar_qk, h * kD, row0);
-        tma_load_2d(sK, &mk, &ctl.bar_qk, h * kD, row0);
-    };
-    auto load_v = [&](int w) {
-        const int item = w / a.H, h = w - item * a.H;
-        const int row0 = __ldg(a.cu + a.plan[2 + item]);
-        mbar_expect_tx(&ctl.bar_v, 16384);
-        tma_load_2d(sV, &mv, &ctl.bar_v, h * kD, row0);
-    };
-
+    VlUnit u{0, 0, 0}, un{0, 0, 0};
+    if ((int)blockIdx.x < n_units) u = vl_unit(a, blockIdx.x);
     if (tid == 0 && (int)blockIdx.x < n_units) {
-        load_qk(blockIdx.x);
-        load_v(blockIdx.x);
+        mbar_expect_tx(&ctl.bar_qk, 32768);
+        tma_load_2d(sQ, &mq, &ctl.bar_qk, u.h * kD, u.row0);
+        tma_load_2d(sK, &mk, &ctl.bar_qk, u.h * kD, u.row0);
+        mbar_expect_tx(&ctl.bar_v, 16384);
+        tma_load_2d(sV, &mv, &ctl.bar_v, u.h * kD, u.row0);
     }
 
     int it = 0;
-    for (int w = blockIdx.x; w < n_units; w += gridDim.x, ++it) {
+    for (int w = blockIdx.x; w < n_units; w += gridDim.x, ++it, u = un) {
         const uint32_t par = it & 1;
-        const VlUnit u = vl_unit(a, w, tid);
-        const int nch = (u.nrows + 31) >> 5;
-        const bool warp_live = __any_sync(0xffffffffu, u.valid);
         const int w_next = w + gridDim.x;
+        const bool has_next = w_next < n_units;
+        if (has_next) un = vl_unit(a, w_next);  // the next unit's header: its loads complete under this unit's work
+        const bool valid = r < u.nrows;
+        int lo = 0, hi = 0;
+        if (valid) {
+            const int32_t win = __ldg(rowwin + u.row0 + r);
+            lo = win & 0xffff, hi = win >> 16;
+        }
+        const int nch = (u.nrows + 31) >> 5;
+        const bool warp_live = (warp & 3) * 32 < u.nrows;
 
         if (tid == 0) {
             mbar_wait(&ctl.bar_qk, par);
@@ -184,63 +200,87 @@ __global__ void __launch_bounds__(kVlThreads, 2)
         __syncwarp();
         mbar_wait(&ctl.bar_s, par);
         tc_fence_after();
-        if (tid == 0 && w_next < n_units) load_qk(w_next);  // Q, K are free: the next unit's tiles fly under this softmax
+        if (tid == 0 && has_next) {  // Q, K are free: the next unit's tiles fly under this softmax
+            mbar_expect_tx(&ctl.bar_qk, 32768);
+            tma_load_2d(sQ, &mq, &ctl.bar_qk, un.h * kD, un.row0);
+            tma_load_2d(sK, &mk, &ctl.bar_qk, un.h * kD, un.row0);
+        }
         __syncwarp();
 
-        float m = neg_inf(), l = 0.f;
+        // ---- this thread's <= 64 scores (chunks 2 hf, 2 hf + 1): masking only in chunks the window [lo, hi) cuts through
+        float x[64];
+        uint32_t bits[2] = {0u, 0u};
+        float mloc = neg_inf();
         if (warp_live) {
-            // ---- pass 1: row maximum over the row's window (log2 units)
-            for (int c = 0; c < nch; ++c) {
-                float x[32];
-                tmem_ld_32x32(lane_base + c * 32, reinterpret_cast<uint32_t *>(x));
-                tmem_wait_ld();
-                const uint32_t bits = window_bits(u.lo, u.hi, c);
-                if (bits == 0u) continue;
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+                if (2 * hf + j < nch) tmem_ld_32x32(lane_base + (2 * hf + j) * 32, reinterpret_cast<uint32_t *>(x) + j * 32);
+            tmem_wait_ld();
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                const int c = 2 * hf + j;
+                bits[j] = c < nch ? window_bits(lo, hi, c) : 0u;
+                if (bits[j] == 0u) continue;
+                if (bits[j] != 0xffffffffu) {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i)
+                        if (!((bits[j] >> i) & 1u)) x[j * 32 + i] = neg_inf();
+                }
                 float mx0 = neg_inf(), mx1 = neg_inf();
 #pragma unroll
-                for (int i = 0; i < 32; i += 2) {
-                    mx0 = fmaxf(mx0, (bits >> i) & 1u ? x[i] : neg_inf());
-                    mx1 = fmaxf(mx1, (bits >> (i + 1)) & 1u ? x[i + 1] : neg_inf());
+                for (int i = 0; i < 32; i += 4) {
+                    mx0 = fmax3(mx0, x[j * 32 + i], x[j * 32 + i + 1]);
+                    mx1 = fmax3(mx1, x[j * 32 + i + 2], x[j * 32 + i + 3]);
                 }
-                m = fmaxf(m, fmaxf(mx0, mx1));
+                mloc = fmax3(mloc, mx0, mx1);
             }
-            m *= a.scale_log2;
+        }
+        ctl.xmax[hf][r] = mloc;
+        __syncthreads();
+        const float m = fmaxf(mloc, ctl.xmax[hf ^ 1][r]) * a.scale_log2;
+        float lpart = 0.f;
+        if (warp_live) {
             const float nm = (m == neg_inf()) ? 0.f : -m;
             const float sl2 = a.scale_log2;
             const uint32_t salt = drop_salt(a.drop, (uint32_t)w);
-            // ---- pass 2: p = 2^(x log2e - m), row sum, dropout, bf16 P tile (K-major A operand of P V)
-            for (int c = 0; c < nch; ++c) {
-                float x[32];
-                tmem_ld_32x32(lane_base + c * 32, reinterpret_cast<uint32_t *>(x));
-                tmem_wait_ld();
-                const uint32_t bits = window_bits(u.lo, u.hi, c);
-                float sum0 = 0.f, sum1 = 0.f;
+            float sum0 = 0.f, sum1 = 0.f;
 #pragma unroll
-                for (int i = 0; i < 32; i += 2) {
-                    float p0 = (bits >> i) & 1u ? ex2(fmaf(x[i], sl2, nm)) : 0.f;
-                    float p1 = (bits >> (i + 1)) & 1u ? ex2(fmaf(x[i + 1], sl2, nm)) : 0.f;
-                    sum0 += p0;  // the row sum is of the undropped p
-                    sum1 += p1;
-                    if (a.drop.thr16) {
-                        const uint32_t hp = drop_hash(salt, (uint32_t)(tid * 128 + c * 32 + i));
-                        p0 = (hp >> 16) >= a.drop.thr16 ? p0 * a.drop.scale : 0.f;
-                        p1 = (hp & 0xffffu) >= a.drop.thr16 ? p1 * a.drop.scale : 0.f;
-                    }
-                    x[i] = p0;
-                    x[i + 1] = p1;
+            for (int j = 0; j < 2; ++j) {
+                const int c = 2 * hf + j;
+                if (c >= nch) continue;
+                uint8_t *prow = sP + hf * 16384;
+                if (bits[j] == 0u) {
+#pragma unroll
+                    for (int ch = 0; ch < 4; ++ch)
+                        *reinterpret_cast<uint4 *>(prow + sw128_offset(r, j * 4 + ch)) = make_uint4(0, 0, 0, 0);
+                    continue;
                 }
-                l += sum0 + sum1;
+                float *xc = x + j * 32;
+#pragma unroll
+                for (int i = 0; i < 32; i += 2) {   // masked entries are -inf: 2^(-inf) = 0, no select
+                    ffma2(xc[i], xc[i + 1], xc[i], xc[i + 1], sl2, sl2, nm, nm);
+                    xc[i] = ex2(xc[i]);
+                    xc[i + 1] = ex2(xc[i + 1]);
+                    fadd2(sum0, sum1, sum0, sum1, xc[i], xc[i + 1]);   // the row sum is of the undropped p
+                    if (a.drop.thr16) {
+                        const uint32_t hp = drop_hash(salt, (uint32_t)(r * 128 + c * 32 + i));
+                        xc[i] = (hp >> 16) >= a.drop.thr16 ? xc[i] * a.drop.scale : 0.f;
+                        xc[i + 1] = (hp & 0xffffu) >= a.drop.thr16 ? xc[i + 1] * a.drop.scale : 0.f;
+                    }
+                }
 #pragma unroll
                 for (int ch = 0; ch < 4; ++ch) {
                     uint4 v;
-                    v.x = pack_bf16x2(x[ch * 8 + 0], x[ch * 8 + 1]);
-                    v.y = pack_bf16x2(x[ch * 8 + 2], x[ch * 8 + 3]);
-                    v.z = pack_bf16x2(x[ch * 8 + 4], x[ch * 8 + 5]);
-                    v.w = pack_bf16x2(x[ch * 8 + 6], x[ch * 8 + 7]);
-                    *reinterpret_cast<uint4 *>(sP + (c >> 1) * 16384 + sw128_offset(tid, (c & 1) * 4 + ch)) = v;
+                    v.x = pack_bf16x2(xc[ch * 8 + 0], xc[ch * 8 + 1]);
+                    v.y = pack_bf16x2(xc[ch * 8 + 2], xc[ch * 8 + 3]);
+                    v.z = pack_bf16x2(xc[ch * 8 + 4], xc[ch * 8 + 5]);
+                    v.w = pack_bf16x2(xc[ch * 8 + 6], xc[ch * 8 + 7]);
+                    *reinterpret_cast<uint4 *>(prow + sw128_offset(r, j * 4 + ch)) = v;
                 }
             }
+            lpart = sum0 + sum1;
         }
+        ctl.xsum[hf][r] = lpart;
         fence_proxy_async();
         tc_fence_before();
         __syncthreads();
@@ -255,21 +295,24 @@ __global__ void __launch_bounds__(kVlThreads, 2)
             umma_commit(&ctl.bar_o);
         }
         __syncwarp();
+        const float l = lpart + ctl.xsum[hf ^ 1][r];
         mbar_wait(&ctl.bar_o, par);
         tc_fence_after();
-        if (tid == 0 && w_next < n_units) load_v(w_next);  // V and P are free
+        if (tid == 0 && has_next) {  // V and P are free
+            mbar_expect_tx(&ctl.bar_v, 16384);
+            tma_load_2d(sV, &mv, &ctl.bar_v, un.h * kD, un.row0);
+        }
         __syncwarp();
         if (warp_live) {
-            float o[64];
-            tmem_ld_32x32(lane_base + 128, reinterpret_cast<uint32_t *>(o));
-            tmem_ld_32x32(lane_base + 160, reinterpret_cast<uint32_t *>(o) + 32);
+            float o[32];
+            tmem_ld_32x32(lane_base + 128 + hf * 32, reinterpret_cast<uint32_t *>(o));
             tmem_wait_ld();
-            if (u.valid) {
+            if (valid) {
                 const float inv = l > 0.f ? 1.f / l : 0.f;
-                const size_t g = (size_t)(u.row0 + tid);
-                __nv_bfloat16 *op = a.out + g * a.o_stride + (size_t)u.h * kD;
+                const size_t g = (size_t)(u.row0 + r);
+                __nv_bfloat16 *op = a.out + g * a.o_stride + (size_t)u.h * kD + hf * 32;
 #pragma unroll
-                for (int ch = 0; ch < 8; ++ch) {
+                for (int ch = 0; ch < 4; ++ch) {
                     uint4 v;
                     v.x = pack_bf16x2(o[ch * 8 + 0] * inv, o[ch * 8 + 1] * inv);
                     v.y = pack_bf16x2(o[ch * 8 + 2] * inv, o[ch * 8 + 3] * inv);
@@ -277,10 +320,10 @@ __global__ void __launch_bounds__(kVlThreads, 2)
                     v.w = pack_bf16x2(o[ch * 8 + 6] * inv, o[ch * 8 + 7] * inv);
                     reinterpret_cast<uint4 *>(op)[ch] = v;
                 }
-                if (a.lse) a.lse[(size_t)u.h * a.total + g] = l > 0.f ? m * kLn2 + logf(l) : __int_as_float(0x7f800000);
+                if (a.lse && hf == 0) a.lse[(size_t)u.h * a.total + g] = l > 0.f ? m * kLn2 + logf(l) : __int_as_float(0x7f800000);
             }
         }
-        tc_fence_before();  // S / O columns are rewritten by the next unit's MMAs (issued after the next __syncthreads / by tid 0 in order)
+        tc_fence_before();  // the S / O columns and the exchange words are rewritten by the next unit
         __syncthreads();
     }
     tc_fence_before();
@@ -295,7 +338,7 @@ struct VlBwdCtrl {
 };
 // Q | K | dO | P (32 KB: its second half is the V tile, dead once dP = dO V^T has completed) | dS
 constexpr int kVlBwdTiles = 3 * 16384 + 32768 + 32768;
-constexpr int kVlBwdSmem = kVlBwdTiles + 64;
+constexpr int kVlBwdSmem = kVlBwdTiles + 64;  // 2 CTAs / SM: 2 x (112 KB + 64 B + 1 KB reserved) <= 228 KB
 
 __global__ void __launch_bounds__(kVlThreads, 2)
     attn_varlen_bwd_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__ CUtensorMap mk,
@@ -304,8 +347,10 @@ __global__ void __launch_bounds__(kVlThreads, 2)
     uint8_t *sQ = smem, *sK = smem + 16384, *sdO = smem + 32768, *sP = smem + 49152, *sV = smem + 65536, *sdS = smem + 81920;
     VlBwdCtrl &ctl = *reinterpret_cast<VlBwdCtrl *>(smem + kVlBwdTiles);
     const int tid = threadIdx.x, warp = tid >> 5;
+    const int r = tid & 127, hf = tid >> 7;
     const int n_items = a.plan[0];
     const int n_units = a.plan[1] ? 0 : n_items * a.H;
+    const int32_t *rowwin = a.plan + plan_rows_off(a.n_seq);
 
     if (tid == 0) {
         if (smem_u32(smem) & 1023u) __trap();
@@ -326,46 +371,47 @@ __global__ void __launch_bounds__(kVlThreads, 2)
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = ctl.tmem_base;
-    const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
+    const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
     constexpr uint32_t cS = 0, cDP = 128, cDV = 0, cDK = 64, cDQ = 128;  // dV / dK / dQ reuse the S / dP columns
     const uint32_t idesc_s = idesc_bf16(128, 128, 0, 0);
     const uint32_t idesc_kv = idesc_bf16(128, 64, 1, 1);  // A = P / dS read MN-major (M = key), B = dO / Q MN-major
     const uint32_t idesc_dq = idesc_bf16(128, 64, 0, 1);  // A = dS K-major (M = query), B = K MN-major
 
+    auto load_unit = [&](const VlUnit &x) {  // tid 0: the four operand tiles of a unit
+        mbar_expect_tx(&ctl.bar_ld, 65536);
+        tma_load_2d(sQ, &mq, &ctl.bar_ld, x.h * kD, x.row0);
+        tma_load_2d(sK, &mk, &ctl.bar_ld, x.h * kD, x.row0);
+        tma_load_2d(sV, &mv, &ctl.bar_ld, x.h * kD, x.row0);
+        tma_load_2d(sdO, &mdo, &ctl.bar_ld, x.h * kD, x.row0);
+    };
+    VlUnit u{0, 0, 0}, un{0, 0, 0};
+    if ((int)blockIdx.x < n_units) u = vl_unit(a, blockIdx.x);
+    if (tid == 0 && (int)blockIdx.x < n_units) load_unit(u);
+    int32_t win_c = 0;
+    float lse_c = 0.f;
+    if ((int)blockIdx.x < n_units && r < u.nrows) {
+        win_c = __ldg(rowwin + u.row0 + r);
+        lse_c = __ldg(a.lse + (size_t)u.h * a.total + u.row0 + r);
+    }
+
     int it = 0;
-    for (int w = blockIdx.x; w < n_units; w += gridDim.x, ++it) {
+    for (int w = blockIdx.x; w < n_units; w += gridDim.x, ++it, u = un) {
         const uint32_t par = it & 1;
-        const VlUnit u = vl_unit(a, w, tid);
+        const int w_next = w + gridDim.x;
+        const bool has_next = w_next < n_units;
+        if (has_next) un = vl_unit(a, w_next);
+        const bool valid = r < u.nrows;
         const int nch = (u.nrows + 31) >> 5;
-        const bool row_used = tid < 32 * nch;  // rows the dV / dK k-steps read: live or zero
-        const bool warp_used = (warp * 32) < 32 * nch;
-        if (tid == 0) {
-            mbar_expect_tx(&ctl.bar_ld, 65536);
-            tma_load_2d(sQ, &mq, &ctl.bar_ld, u.h * kD, u.row0);
-            tma_load_2d(sK, &mk, &ctl.bar_ld, u.h * kD, u.row0);
-            tma_load_2d(sV, &mv, &ctl.bar_ld, u.h * kD, u.row0);
-            tma_load_2d(sdO, &mdo, &ctl.bar_ld, u.h * kD, u.row0);
-        }
-        // ---- delta = rowsum(dO * O), -lse in log2 units: global loads under the TMA latency
-        float delta = 0.f, nlse = neg_inf();
-        if (u.valid) {
-            const size_t g = (size_t)(u.row0 + tid);
-            const uint4 *po = reinterpret_cast<const uint4 *>(a.o_in + g * a.o_stride + (size_t)u.h * kD);
-            const uint4 *pg = reinterpret_cast<const uint4 *>(a.dout + g * a.g_stride + (size_t)u.h * kD);
-#pragma unroll
-            for (int ch = 0; ch < 8; ++ch) {
-                const uint4 x = __ldg(po + ch), y = __ldg(pg + ch);
-                const __nv_bfloat162 *px = reinterpret_cast<const __nv_bfloat162 *>(&x);
-                const __nv_bfloat162 *py = reinterpret_cast<const __nv_bfloat162 *>(&y);
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const float2 fx = __bfloat1622float2(px[i]), fy = __bfloat1622float2(py[i]);
-                    delta = fmaf(fx.x, fy.x, delta);
-                    delta = fmaf(fx.y, fy.y, delta);
-                }
-            }
-            const float lse = a.lse[(size_t)u.h * a.total + g];
-            nlse = (lse == __int_as_float(0x7f800000)) ? neg_inf() : -lse * kLog2e;  // +inf marks a row without keys
+        const bool warp_used = (warp & 3) < nch;  // rows the dV / dK k-steps read (live, or zero-filled): rows [0, 32 nch)
+        // ---- row window and -lse (log2 units) of this row: requested one unit ahead (win_n / lse_n below)
+        const int lo = valid ? (win_c & 0xffff) : 0, hi = valid ? (win_c >> 16) : 0;
+        const float nlse = (!valid || lse_c == __int_as_float(0x7f800000)) ? neg_inf() : -lse_c * kLog2e;  // +inf: a row without keys
+        int32_t win_n = 0;
+        float lse_n = 0.f;
+        if (has_next && r < un.nrows) {
+            const size_t gn = (size_t)(un.row0 + r);
+            win_n = __ldg(rowwin + gn);
+            lse_n = __ldg(a.lse + (size_t)un.h * a.total + gn);
         }
         if (tid == 0) {
             mbar_wait(&ctl.bar_ld, par);
@@ -383,31 +429,88 @@ __global__ void __launch_bounds__(kVlThreads, 2)
         mbar_wait(&ctl.bar_s, par);
         tc_fence_after();
         __syncwarp();
+        // ---- pass A: delta = rowsum(dO * O) = sum_k keep P dP / (1 - p_drop) over the row's window -- from S and dP alone,
+        // no O / dO rows from global memory (their DRAM latency sat on every unit's critical path, and 25 % of the traffic)
+        const uint32_t salt = drop_salt(a.drop, (uint32_t)w);
+        const float sl2 = a.scale_log2, sc = a.scale;
+        float dpart = 0.f;
         if (warp_used) {
-            const uint32_t salt = drop_salt(a.drop, (uint32_t)w);
-            const float sl2 = a.scale_log2, sc = a.scale;
-            for (int c = 0; c < nch; ++c) {
+#pragma unroll 1
+            for (int j = 0; j < 2; ++j) {
+                const int c = 2 * hf + j;
+                if (c >= nch) break;   // uniform across the warp
+                const uint32_t bits = window_bits(lo, hi, c);
+                if (!__any_sync(0xffffffffu, bits != 0u)) continue;   // warp-uniform
                 float st[32], dp[32];
                 tmem_ld_32x32(lane_base + cS + c * 32, reinterpret_cast<uint32_t *>(st));
                 tmem_ld_32x32(lane_base + cDP + c * 32, reinterpret_cast<uint32_t *>(dp));
                 tmem_wait_ld();
-                const uint32_t bits = window_bits(u.lo, u.hi, c);  // 0 for rows past the item: P = dS = 0
+                if (bits != 0u) {
+                    float a0 = 0.f, a1 = 0.f;
 #pragma unroll
-                for (int i = 0; i < 32; i += 2) {
-                    float p0 = (bits >> i) & 1u ? ex2(fmaf(st[i], sl2, nlse)) : 0.f;
-                    float p1 = (bits >> (i + 1)) & 1u ? ex2(fmaf(st[i + 1], sl2, nlse)) : 0.f;
-                    float k0 = 1.f, k1 = 1.f;
-                    if (a.drop.thr16) {
-                        const uint32_t hp = drop_hash(salt, (uint32_t)(tid * 128 + c * 32 + i));
-                        k0 = (hp >> 16) >= a.drop.thr16 ? a.drop.scale : 0.f;
-                        k1 = (hp & 0xffffu) >= a.drop.thr16 ? a.drop.scale : 0.f;
+                    for (int i = 0; i < 32; i += 2) {
+                        float p0 = (bits >> i) & 1u ? ex2(fmaf(st[i], sl2, nlse)) : 0.f;
+                        float p1 = (bits >> (i + 1)) & 1u ? ex2(fmaf(st[i + 1], sl2, nlse)) : 0.f;
+                        if (a.drop.thr16) {
+                            const uint32_t hp = drop_hash(salt, (uint32_t)(r * 128 + c * 32 + i));
+                            p0 = (hp >> 16) >= a.drop.thr16 ? p0 * a.drop.scale : 0.f;
+                            p1 = (hp & 0xffffu) >= a.drop.thr16 ? p1 * a.drop.scale : 0.f;
+                        }
+                        a0 = fmaf(p0, dp[i], a0);
+                        a1 = fmaf(p1, dp[i + 1], a1);
                     }
-                    dp[i] = p0 * (dp[i] * k0 - delta) * sc;       // d(scaled score) * scale = d(q k^T)
-                    dp[i + 1] = p1 * (dp[i + 1] * k1 - delta) * sc;
-                    st[i] = p0 * k0;
-                    st[i + 1] = p1 * k1;
+                    dpart += a0 + a1;
                 }
-                if (row_used) {
+                __syncwarp();
+            }
+        }
+        // the halves of a row exchange their partial sums through the dS tile (free until pass B): each thread's word lies
+        // inside the bytes only its READER overwrites later (row r of the reader's half), so one barrier is enough
+        *reinterpret_cast<float *>(sdS + (hf ^ 1) * 16384 + sw128_offset(r, 0)) = dpart;
+        __syncthreads();
+        const float delta = dpart + *reinterpret_cast<const float *>(sdS + hf * 16384 + sw128_offset(r, 0));
+        if (warp_used) {
+            const float nds = -delta * sc;   // dS * scale = p * (keep * dP * scale - delta * scale): d(q k^T), not d(scaled score)
+#pragma unroll 1
+            for (int j = 0; j < 2; ++j) {
+                const int c = 2 * hf + j;
+                if (c >= nch) break;   // uniform across the warp
+                const uint32_t bits = window_bits(lo, hi, c);  // 0 for rows past the item and for the other sequences' columns
+                const uint32_t off0 = hf * 16384;
+                float st[32], dp[32];   // warp-collective TMEM reads: every lane, whatever its window
+                tmem_ld_32x32(lane_base + cS + c * 32, reinterpret_cast<uint32_t *>(st));
+                tmem_ld_32x32(lane_base + cDP + c * 32, reinterpret_cast<uint32_t *>(dp));
+                tmem_wait_ld();
+                if (bits == 0u) {   // per-thread branch: no warp-collective operation until both sides have rejoined
+#pragma unroll
+                    for (int ch = 0; ch < 4; ++ch) {
+                        const uint32_t off = off0 + sw128_offset(r, j * 4 + ch);
+                        *reinterpret_cast<uint4 *>(sP + off) = make_uint4(0, 0, 0, 0);
+                        *reinterpret_cast<uint4 *>(sdS + off) = make_uint4(0, 0, 0, 0);
+                    }
+                } else {
+                    if (bits != 0xffffffffu) {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i)
+                            if (!((bits >> i) & 1u)) st[i] = neg_inf();   // p = 2^(-inf) = 0 and dS = 0 * finite = 0
+                    }
+#pragma unroll
+                    for (int i = 0; i < 32; i += 2) {
+                        ffma2(st[i], st[i + 1], st[i], st[i + 1], sl2, sl2, nlse, nlse);
+                        st[i] = ex2(st[i]);
+                        st[i + 1] = ex2(st[i + 1]);
+                        if (a.drop.thr16) {
+                            const uint32_t hp = drop_hash(salt, (uint32_t)(r * 128 + c * 32 + i));
+                            const float k0 = (hp >> 16) >= a.drop.thr16 ? a.drop.scale : 0.f;
+                            const float k1 = (hp & 0xffffu) >= a.drop.thr16 ? a.drop.scale : 0.f;
+                            ffma2(dp[i], dp[i + 1], dp[i], dp[i + 1], k0 * sc, k1 * sc, nds, nds);
+                            fmul2(dp[i], dp[i + 1], dp[i], dp[i + 1], st[i], st[i + 1]);
+                            fmul2(st[i], st[i + 1], st[i], st[i + 1], k0, k1);
+                        } else {
+                            ffma2(dp[i], dp[i + 1], dp[i], dp[i + 1], sc, sc, nds, nds);
+                            fmul2(dp[i], dp[i + 1], dp[i], dp[i + 1], st[i], st[i + 1]);
+                        }
+                    }
 #pragma unroll
                     for (int ch = 0; ch < 4; ++ch) {
                         uint4 vp, vd;
@@ -419,11 +522,12 @@ __global__ void __launch_bounds__(kVlThreads, 2)
                         vd.y = pack_bf16x2(dp[ch * 8 + 2], dp[ch * 8 + 3]);
                         vd.z = pack_bf16x2(dp[ch * 8 + 4], dp[ch * 8 + 5]);
                         vd.w = pack_bf16x2(dp[ch * 8 + 6], dp[ch * 8 + 7]);
-                        const uint32_t off = (c >> 1) * 16384 + sw128_offset(tid, (c & 1) * 4 + ch);
+                        const uint32_t off = off0 + sw128_offset(r, j * 4 + ch);
                         *reinterpret_cast<uint4 *>(sP + off) = vp;   // half 1 of P overwrites the V tile (dP has completed)
                         *reinterpret_cast<uint4 *>(sdS + off) = vd;
                     }
                 }
+                __syncwarp();
             }
         }
         fence_proxy_async();
@@ -448,33 +552,29 @@ __global__ void __launch_bounds__(kVlThreads, 2)
         __syncwarp();
         mbar_wait(&ctl.bar_o, par);
         tc_fence_after();
+        // every shared-memory tile has been consumed by the MMAs: the next unit's loads fly under this unit's epilogue
+        if (tid == 0 && has_next) load_unit(un);
         __syncwarp();
-        if (__any_sync(0xffffffffu, u.valid)) {
-            const size_t g = (size_t)(u.row0 + tid);
+        if ((warp & 3) * 32 < u.nrows) {
+            const size_t g = (size_t)(u.row0 + r);
 #pragma unroll
             for (int which = 0; which < 3; ++which) {
-                float acc[64];
-                const uint32_t col = which == 0 ? cDV : (which == 1 ? cDK : cDQ);
-                tmem_ld_32x32(lane_base + col, reinterpret_cast<uint32_t *>(acc));
-                tmem_ld_32x32(lane_base + col + 32, reinterpret_cast<uint32_t *>(acc) + 32);
+                float acc[32];
+                tmem_ld_32x32(lane_base + (which == 0 ? cDV : (which == 1 ? cDK : cDQ)) + hf * 32, reinterpret_cast<uint32_t *>(acc));
                 tmem_wait_ld();
-                if (u.valid) {
+                if (valid) {
                     __nv_bfloat16 *p = which == 0 ? a.dv + g * a.dv_stride : (which == 1 ? a.dk + g * a.dk_stride : a.dq + g * a.dq_stride);
-                    p += (size_t)u.h * kD;
+                    uint4 *dst = reinterpret_cast<uint4 *>(p + (size_t)u.h * kD + hf * 32);
 #pragma unroll
-                    for (int ch = 0; ch < 8; ++ch) {
-                        uint4 v;
-                        v.x = pack_bf16x2(acc[ch * 8 + 0], acc[ch * 8 + 1]);
-                        v.y = pack_bf16x2(acc[ch * 8 + 2], acc[ch * 8 + 3]);
-                        v.z = pack_bf16x2(acc[ch * 8 + 4], acc[ch * 8 + 5]);
-                        v.w = pack_bf16x2(acc[ch * 8 + 6], acc[ch * 8 + 7]);
-                        reinterpret_cast<uint4 *>(p)[ch] = v;
-                    }
+                    for (int ch = 0; ch < 4; ++ch)
+                        dst[ch] = make_uint4(pack_bf16x2(acc[ch * 8 + 0], acc[ch * 8 + 1]), pack_bf16x2(acc[ch * 8 + 2], acc[ch * 8 + 3]),
+                                             pack_bf16x2(acc[ch * 8 + 4], acc[ch * 8 + 5]), pack_bf16x2(acc[ch * 8 + 6], acc[ch * 8 + 7]));
                 }
             }
         }
+        win_c = win_n, lse_c = lse_n;
         tc_fence_before();
-        __syncthreads();  // every operand tile and TMEM column of this unit is free for the next one
+        __syncthreads();  // every TMEM column and the exchange words of this unit are free for the next one
     }
     tc_fence_before();
     __syncthreads();
@@ -501,20 +601,22 @@ static int units_grid(int n_seq, int H) {
 using namespace mdt;
 using namespace mdt::attn;
 
-extern "C" int mdt_varlen_attn_plan(const int32_t *cu_seqlens, int n_seq, int group, int32_t *plan, mdt_stream_t stream) {
+extern "C" int64_t mdt_varlen_attn_plan_words(int n_seq, int total) { return (int64_t)plan_rows_off(n_seq) + total; }
+
+extern "C" int mdt_varlen_attn_plan(const int32_t *cu_seqlens, int n_seq, int total, int group, int32_t *plan, mdt_stream_t stream) {
     if (int rc = require_sm100()) return rc;
-    MDT_REQUIRE(cu_seqlens && plan && n_seq >= 1, "mdt_varlen_attn_plan: cu_seqlens, plan must be non-null and n_seq >= 1");
-    varlen_plan_kernel<<<1, 32, 0, as_stream(stream)>>>(cu_seqlens, n_seq, group, plan);
+    MDT_REQUIRE(cu_seqlens && plan && n_seq >= 1 && total >= 1, "mdt_varlen_attn_plan: cu_seqlens, plan must be non-null, n_seq and total >= 1");
+    varlen_plan_kernel<<<1, 1024, 0, as_stream(stream)>>>(cu_seqlens, n_seq, group, plan);
     MDT_CHECK_CUDA(cudaGetLastError());
     return MDT_OK;
 }
 
 extern "C" int mdt_varlen_attn_fwd(const void *q, const void *k, const void *v, int64_t q_stride, int64_t k_stride,
-                                   int64_t v_stride, int total, int H, const int32_t *cu_seqlens, int n_seq,
-                                   const int32_t *plan, void *out, int64_t o_stride, float *lse, float softmax_scale,
-                                   float dropout_p, uint64_t dropout_seed, mdt_stream_t stream) {
+                                   int64_t v_stride, int total, int H, int n_seq, const int32_t *plan, void *out,
+                                   int64_t o_stride, float *lse, float softmax_scale, float dropout_p,
+                                   uint64_t dropout_seed, mdt_stream_t stream) {
     if (int rc = require_sm100()) return rc;
-    MDT_REQUIRE(q && k && v && out && lse && cu_seqlens && plan, "mdt_varlen_attn_fwd: null pointer");
+    MDT_REQUIRE(q && k && v && out && lse && plan, "mdt_varlen_attn_fwd: null pointer");
     MDT_REQUIRE(total >= 1 && H >= 1 && n_seq >= 1, "mdt_varlen_attn_fwd: total, H, n_seq must be >= 1");
     MDT_REQUIRE(((uintptr_t)out & 15) == 0 && o_stride % 8 == 0, "mdt_varlen_attn_fwd: out must be 16-byte aligned, stride a multiple of 8");
     MDT_REQUIRE(dropout_p >= 0.f && dropout_p < 1.f, "mdt_varlen_attn_fwd: dropout_p must be in [0, 1)");
@@ -524,7 +626,7 @@ extern "C" int mdt_varlen_attn_fwd(const void *q, const void *k, const void *v, 
     if (int rc = make_rows_map(&mk, k, total, H, k_stride)) return rc;
     if (int rc = make_rows_map(&mv, v, total, H, v_stride)) return rc;
     VarlenArgs a{};
-    a.total = total, a.H = H, a.cu = cu_seqlens, a.plan = plan;
+    a.total = total, a.H = H, a.n_seq = n_seq, a.plan = plan;
     a.out = reinterpret_cast<__nv_bfloat16 *>(out), a.o_stride = o_stride, a.lse = lse;
     a.scale = softmax_scale, a.scale_log2 = softmax_scale * kLog2e;
     a.drop = make_drop(dropout_p, dropout_seed);
@@ -536,12 +638,11 @@ extern "C" int mdt_varlen_attn_fwd(const void *q, const void *k, const void *v, 
 
 extern "C" int mdt_varlen_attn_bwd(const void *q, const void *k, const void *v, int64_t q_stride, int64_t k_stride,
                                    int64_t v_stride, const void *out, int64_t o_stride, const void *grad_out,
-                                   int64_t g_stride, const float *lse, int total, int H, const int32_t *cu_seqlens,
-                                   int n_seq, const int32_t *plan, void *dq, void *dk, void *dv, int64_t dq_stride,
-                                   int64_t dk_stride, int64_t dv_stride, float softmax_scale, float dropout_p,
-                                   uint64_t dropout_seed, mdt_stream_t stream) {
+                                   int64_t g_stride, const float *lse, int total, int H, int n_seq, const int32_t *plan,
+                                   void *dq, void *dk, void *dv, int64_t dq_stride, int64_t dk_stride, int64_t dv_stride,
+                                   float softmax_scale, float dropout_p, uint64_t dropout_seed, mdt_stream_t stream) {
     if (int rc = require_sm100()) return rc;
-    MDT_REQUIRE(q && k && v && out && grad_out && lse && cu_seqlens && plan && dq && dk && dv, "mdt_varlen_attn_bwd: null pointer");
+    MDT_REQUIRE(q && k && v && out && grad_out && lse && plan && dq && dk && dv, "mdt_varlen_attn_bwd: null pointer");
     MDT_REQUIRE(total >= 1 && H >= 1 && n_seq >= 1, "mdt_varlen_attn_bwd: total, H, n_seq must be >= 1");
     for (int64_t s : {o_stride, g_stride, dq_stride, dk_stride, dv_stride})
         MDT_REQUIRE(s % 8 == 0, "mdt_varlen_attn_bwd: strides must be multiples of 8 elements");
@@ -555,7 +656,7 @@ extern "C" int mdt_varlen_attn_bwd(const void *q, const void *k, const void *v, 
     if (int rc = make_rows_map(&mv, v, total, H, v_stride)) return rc;
     if (int rc = make_rows_map(&mdo, grad_out, total, H, g_stride)) return rc;
     VarlenArgs a{};
-    a.total = total, a.H = H, a.cu = cu_seqlens, a.plan = plan;
+    a.total = total, a.H = H, a.n_seq = n_seq, a.plan = plan;
     a.lse = const_cast<float *>(lse);
     a.scale = softmax_scale, a.scale_log2 = softmax_scale * kLog2e;
     a.drop = make_drop(dropout_p, dropout_seed);

@@ -60,13 +60,13 @@ class TextPack:
         # the same sequences without bottleneck slots (the trunk layers in front of the fusion stack)
         cu0 = torch.zeros(n + 1, dtype=torch.int64, device=dev)
         cu0[1:] = torch.cumsum(lens, 0)
-        self.text_only = _SeqLens(cu0.to(torch.int32), text_max)
+        self.text_only = _SeqLens(cu0.to(torch.int32), text_max, text_tokens)
 
     @property
     def plan(self):
         """Tile plan of the packed attention kernel (csrc/attn_varlen.cu): built once, shared by all layers and passes."""
         if self._plan is None:
-            self._plan = ops.varlen_plan(self.cu_seqlens)
+            self._plan = ops.varlen_plan(self.cu_seqlens, self.total)
         return self._plan
 
     def gather_text(self, text_padded: torch.Tensor) -> torch.Tensor:
@@ -87,14 +87,14 @@ class TextPack:
 
 
 class _SeqLens:
-    def __init__(self, cu_seqlens, max_seqlen):
-        self.cu_seqlens, self.max_seqlen = cu_seqlens, max_seqlen
+    def __init__(self, cu_seqlens, max_seqlen, total):
+        self.cu_seqlens, self.max_seqlen, self.total = cu_seqlens, max_seqlen, total
         self._plan = None
 
     @property
     def plan(self):
         if self._plan is None:
-            self._plan = ops.varlen_plan(self.cu_seqlens)
+            self._plan = ops.varlen_plan(self.cu_seqlens, self.total)
         return self._plan
 
 
@@ -110,7 +110,7 @@ def _varlen_attention(qkv, pack, dropout_p: float):
     if TEXT_ATTN_IMPL == "mdt":
         if pack.max_seqlen > 128:
             raise RuntimeError(f"packed text attention handles sequences of <= 128 rows, got {pack.max_seqlen}")
-        return ops.varlen_attention(qkv, pack.cu_seqlens, pack.plan, dropout_p=dropout_p)
+        return ops.varlen_attention(qkv, pack.plan, dropout_p=dropout_p)
     global _FLASH
     if _FLASH is None:
         from flash_attn import flash_attn_varlen_qkvpacked_func

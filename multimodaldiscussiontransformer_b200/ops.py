@@ -325,73 +325,99 @@ def biased_attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, bias: Op
 # ------------------------------------------------------------------------------------------
 # N1  self-attention over packed (unpadded) sequences     multi_graphormer_fusion_layer.py:105-149
 # ------------------------------------------------------------------------------------------
-def varlen_plan(cu_seqlens: torch.Tensor, group: bool = True) -> torch.Tensor:
-    """Group consecutive sequences into <= 128-row tiles (device-side, no sync): int32 ``[n_seq + 3]``."""
-    _require_cuda(cu_seqlens)
-    lib = _lib.load()
-    assert cu_seqlens.dtype == torch.int32 and cu_seqlens.is_contiguous()
-    n_seq = cu_seqlens.numel() - 1
-    plan = torch.empty(n_seq + 3, dtype=torch.int32, device=cu_seqlens.device)
-    with torch.cuda.device(cu_seqlens.device):
-        _lib.check(lib.mdt_varlen_attn_plan(_lib.ptr(cu_seqlens), n_seq, 1 if group else 0, _lib.ptr(plan), _lib.stream()),
-                   "mdt_varlen_attn_plan")
-    return plan
+class VarlenPlan:
+    """Tile plan of the packed-sequence attention (csrc/attn_varlen.cu): which consecutive sequences share a 128-row
+    tile and every packed row's key window.  Built on the device from ``cu_seqlens`` without a sync; ``total`` (number of
+    packed rows) is host-known like ``max_seqlen`` in any varlen attention API."""
+
+    def __init__(self, cu_seqlens: torch.Tensor, total: int, group: bool = True):
+        _require_cuda(cu_seqlens)
+        lib = _lib.load()
+        assert cu_seqlens.dtype == torch.int32 and cu_seqlens.is_contiguous()
+        self.n_seq, self.total = cu_seqlens.numel() - 1, int(total)
+        self.data = torch.empty(int(lib.mdt_varlen_attn_plan_words(self.n_seq, self.total)), dtype=torch.int32,
+                                device=cu_seqlens.device)
+        with torch.cuda.device(cu_seqlens.device):
+            _lib.check(lib.mdt_varlen_attn_plan(_lib.ptr(cu_seqlens), self.n_seq, self.total, 1 if group else 0,
+                                                _lib.ptr(self.data), _lib.stream()), "mdt_varlen_attn_plan")
+
+    # host-side views (synchronise; tests and diagnostics only)
+    def n_items(self) -> int:
+        return int(self.data[0])
+
+    def error(self) -> bool:
+        return bool(int(self.data[1]))
+
+    def item_rows(self):
+        """first packed row of every item, plus ``total``"""
+        n = self.n_items()
+        return self.data[4:4 + 2 * (n + 1):2].tolist()
+
+    def item_first_seq(self):
+        n = self.n_items()
+        return self.data[5:5 + 2 * (n + 1):2].tolist()
+
+
+def varlen_plan(cu_seqlens: torch.Tensor, total: int, group: bool = True) -> VarlenPlan:
+    return VarlenPlan(cu_seqlens, total, group)
 
 
 class _VarlenAttention(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, qkv, cu_seqlens, plan, dropout_p, seed, scale):
-        _require_cuda(qkv, cu_seqlens, plan)
+    def forward(ctx, qkv, plan, dropout_p, seed, scale):
+        _require_cuda(qkv, plan.data)
         lib = _lib.load()
         if qkv.dtype != torch.bfloat16 or qkv.dim() != 4 or qkv.shape[1] != 3 or qkv.shape[3] != 64:
             raise ValueError(f"qkv must be bf16 [total, 3, H, 64], got {qkv.dtype} {tuple(qkv.shape)}")
         total, _, H, _ = qkv.shape
+        if total != plan.total:
+            raise ValueError(f"the plan was built for {plan.total} packed rows, qkv has {total}")
         if not (qkv.stride(3) == 1 and qkv.stride(2) == 64 and qkv.stride(1) == H * 64 and qkv.stride(0) % 8 == 0
                 and qkv.data_ptr() % 16 == 0):
             qkv = qkv.contiguous()   # rows may be slices of a wider buffer; anything else is compacted
-        n_seq = cu_seqlens.numel() - 1
         out = torch.empty((total, H, 64), dtype=qkv.dtype, device=qkv.device)
         lse = torch.empty((H, total), dtype=torch.float32, device=qkv.device)
         rs = qkv.stride(0)
-        with torch.cuda.device(qkv.device), _timed("vl_fwd", total, H, n_seq):
+        with torch.cuda.device(qkv.device), _timed("vl_fwd", total, H, plan.n_seq):
             _lib.check(lib.mdt_varlen_attn_fwd(_lib.ptr(qkv[:, 0]), _lib.ptr(qkv[:, 1]), _lib.ptr(qkv[:, 2]), rs, rs, rs, total, H,
-                                               _lib.ptr(cu_seqlens), n_seq, _lib.ptr(plan), _lib.ptr(out), H * 64, _lib.ptr(lse),
+                                               plan.n_seq, _lib.ptr(plan.data), _lib.ptr(out), H * 64, _lib.ptr(lse),
                                                float(scale), float(dropout_p), int(seed), _lib.stream()), "mdt_varlen_attn_fwd")
-        ctx.save_for_backward(qkv, out, lse, cu_seqlens, plan)
+        ctx.save_for_backward(qkv, out, lse, plan.data)
+        ctx.plan = plan
         ctx.drop = (float(dropout_p), int(seed), float(scale))
         return out
 
     @staticmethod
     def backward(ctx, grad_out):
-        qkv, out, lse, cu_seqlens, plan = ctx.saved_tensors
+        qkv, out, lse, plan_data = ctx.saved_tensors
+        plan = ctx.plan
         lib = _lib.load()
         total, _, H, _ = qkv.shape
-        n_seq = cu_seqlens.numel() - 1
         go = grad_out.contiguous()
         dqkv = torch.empty((total, 3, H, 64), dtype=qkv.dtype, device=qkv.device)  # every row is written (sequences tile [0, total))
         rs, gs = qkv.stride(0), 3 * H * 64
-        with torch.cuda.device(qkv.device), _timed("vl_bwd", total, H, n_seq):
+        with torch.cuda.device(qkv.device), _timed("vl_bwd", total, H, plan.n_seq):
             _lib.check(lib.mdt_varlen_attn_bwd(_lib.ptr(qkv[:, 0]), _lib.ptr(qkv[:, 1]), _lib.ptr(qkv[:, 2]), rs, rs, rs,
                                                _lib.ptr(out), H * 64, _lib.ptr(go), H * 64, _lib.ptr(lse), total, H,
-                                               _lib.ptr(cu_seqlens), n_seq, _lib.ptr(plan), _lib.ptr(dqkv[:, 0]),
+                                               plan.n_seq, _lib.ptr(plan_data), _lib.ptr(dqkv[:, 0]),
                                                _lib.ptr(dqkv[:, 1]), _lib.ptr(dqkv[:, 2]), gs, gs, gs, ctx.drop[2], ctx.drop[0],
                                                ctx.drop[1], _lib.stream()), "mdt_varlen_attn_bwd")
-        return dqkv, None, None, None, None, None
+        return dqkv, None, None, None, None
 
 
-def varlen_attention(qkv: torch.Tensor, cu_seqlens: torch.Tensor, plan: torch.Tensor, dropout_p: float = 0.0,
-                     seed: Optional[int] = None, softmax_scale: Optional[float] = None) -> torch.Tensor:
+def varlen_attention(qkv: torch.Tensor, plan: VarlenPlan, dropout_p: float = 0.0, seed: Optional[int] = None,
+                     softmax_scale: Optional[float] = None) -> torch.Tensor:
     """Self-attention inside every packed sequence: ``qkv`` bf16 ``[total, 3, H, 64]`` -> ``[total, H, 64]``.
 
-    ``cu_seqlens`` int32 ``[n_seq + 1]`` must tile ``[0, total)`` with sequences of at most 128 rows; ``plan`` comes from
-    ``varlen_plan(cu_seqlens)`` (once per batch).  The scores are scaled by ``softmax_scale`` (default ``64 ** -0.5``)
-    inside the kernels (folded into the exponent), so ``q`` is passed unscaled."""
+    ``plan = varlen_plan(cu_seqlens, total)`` (once per batch): ``cu_seqlens`` int32 ``[n_seq + 1]`` tiles ``[0, total)`` with
+    sequences of at most 128 rows.  The scores are scaled by ``softmax_scale`` (default ``64 ** -0.5``) inside the kernels
+    (folded into the exponent), so ``q`` is passed unscaled."""
     if not 0.0 <= dropout_p < 1.0:
         raise ValueError("dropout_p must be in [0, 1)")
     if seed is None:
         seed = next_seed() if dropout_p > 0.0 else 0
     scale = 64 ** -0.5 if softmax_scale is None else float(softmax_scale)
-    return _VarlenAttention.apply(qkv, cu_seqlens, plan, float(dropout_p), int(seed), scale)
+    return _VarlenAttention.apply(qkv, plan, float(dropout_p), int(seed), scale)
 
 
 # ------------------------------------------------------------------------------------------

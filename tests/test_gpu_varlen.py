@@ -73,20 +73,21 @@ def lens_of(name):
 def test_varlen_forward_backward(ops, name, H, group):
     lens = lens_of(name)
     qkv, cu = make(lens, H, seed=len(lens) + H)
-    plan = ops.varlen_plan(cu, group=group)
-    n_items = int(plan[0])
-    assert int(plan[1]) == 0
-    firsts = plan[2:2 + n_items + 1].tolist()
+    plan = ops.varlen_plan(cu, sum(lens), group=group)
+    n_items = plan.n_items()
+    assert not plan.error()
+    firsts = plan.item_first_seq()
     assert firsts[0] == 0 and firsts[-1] == len(lens) and all(a < b for a, b in zip(firsts, firsts[1:]))
     cul = cu.tolist()
     assert all(cul[b] - cul[a] <= 128 for a, b in zip(firsts, firsts[1:]))
+    assert plan.item_rows() == [cul[s] for s in firsts]
     if not group:
         assert n_items == len(lens)
     elif name == "many_small":
         assert n_items <= 4                                   # 319 rows -> 3 tiles (greedy)
     scale = 64 ** -0.5
     x = qkv.detach().clone().requires_grad_(True)
-    o = ops.varlen_attention(x, cu, plan)
+    o = ops.varlen_attention(x, plan)
     xr = qkv.detach().float().requires_grad_(True)
     o_ref = reference(xr, lens, scale)
     assert o.shape == o_ref.shape and o.dtype == torch.bfloat16
@@ -108,8 +109,8 @@ def test_varlen_strided_rows_and_scale(ops):
     wide = torch.randn(total, 3 * H * 64 + 64, generator=g).bfloat16().cuda()
     qkv = wide[:, :3 * H * 64].view(total, 3, H, 64)          # non-contiguous rows
     cu = torch.tensor([0] + list(torch.tensor(lens).cumsum(0)), dtype=torch.int32).cuda()
-    plan = ops.varlen_plan(cu)
-    o = ops.varlen_attention(qkv, cu, plan, softmax_scale=0.2)
+    plan = ops.varlen_plan(cu, total)
+    o = ops.varlen_attention(qkv, plan, softmax_scale=0.2)
     o_ref = reference(qkv, lens, 0.2)
     assert float((o.float() - o_ref).abs().max()) <= FWD_ATOL
 
@@ -118,8 +119,8 @@ def keep_mask_from_plan(plan, cu, H, seed, p):
     """bool [total, H, 128]: the kernels' counter-hash mask for (packed row, head, tile-local key column)."""
     thr = min(65535, int(p * 65536.0 + 0.5))
     lo, hi = seed & _M32, (seed >> 32) & _M32
-    n_items = int(plan[0])
-    firsts = plan[2:2 + n_items + 1].tolist()
+    n_items = plan.n_items()
+    firsts = plan.item_first_seq()
     cul = cu.tolist()
     total = cul[-1]
     keep = torch.zeros(total, H, 128, dtype=torch.bool)
@@ -151,11 +152,11 @@ def test_varlen_dropout_forward_backward(ops, group):
     lens = lens_of("text_like")[:24] + [128, 3]
     H, p, seed = 4, 0.3, 0x0BAD_5EED_1234
     qkv, cu = make(lens, H, seed=99)
-    plan = ops.varlen_plan(cu, group=group)
-    keep_tile = keep_mask_from_plan(plan.cpu(), cu.cpu(), H, seed, p)       # columns are tile-local
+    plan = ops.varlen_plan(cu, sum(lens), group=group)
+    keep_tile = keep_mask_from_plan(plan, cu.cpu(), H, seed, p)       # columns are tile-local
     # tile-local column of key j of sequence s = (cu[s] - row0 of its item) + j  ->  per-sequence [H, n, n] masks
-    n_items = int(plan[0])
-    firsts = plan[2:2 + n_items + 1].tolist()
+    n_items = plan.n_items()
+    firsts = plan.item_first_seq()
     cul = cu.tolist()
     keep_rows = torch.zeros(sum(lens), H, 128, dtype=torch.bool)
     seq_keep = []
@@ -177,7 +178,7 @@ def test_varlen_dropout_forward_backward(ops, group):
         return torch.cat(outs)
 
     x = qkv.detach().clone().requires_grad_(True)
-    o = ops.varlen_attention(x, cu, plan, dropout_p=p, seed=seed)
+    o = ops.varlen_attention(x, plan, dropout_p=p, seed=seed)
     xr = qkv.detach().float().requires_grad_(True)
     o_ref = ref(xr)
     assert float((o.float() - o_ref).abs().max()) <= 3e-2
@@ -190,8 +191,8 @@ def test_varlen_dropout_forward_backward(ops, group):
 
 def test_varlen_plan_flags_long_sequences(ops):
     cu = torch.tensor([0, 10, 150, 160], dtype=torch.int32).cuda()
-    plan = ops.varlen_plan(cu)
-    assert int(plan[1]) == 1
+    plan = ops.varlen_plan(cu, 160)
+    assert plan.error()
 
 
 def test_varlen_large_batch_matches_reference(ops):
@@ -200,8 +201,8 @@ def test_varlen_large_batch_matches_reference(ops):
     lens = (4 + torch.randint(8, 101, (4096,), generator=g)).tolist()
     H = 12
     qkv, cu = make(lens, H, seed=5)
-    plan = ops.varlen_plan(cu)
-    o = ops.varlen_attention(qkv, cu, plan)
+    plan = ops.varlen_plan(cu, sum(lens))
+    o = ops.varlen_attention(qkv, plan)
     # reference on a sample of sequences (first, last, and every 97th)
     cul = cu.tolist()
     for s in list(range(0, 4096, 97)) + [4095]:
