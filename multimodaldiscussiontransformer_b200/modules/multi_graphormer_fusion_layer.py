@@ -180,6 +180,41 @@ class FusedLayerNorm(nn.LayerNorm):
         return super().forward(x)
 
 
+#: "mdt" = the ViT blocks' self-attention on this library's tcgen05 kernels (bf16 CUDA tensors); "sdpa" = Hugging Face's
+#: default (cuDNN / flash SDPA), kept as the A/B comparison (MDT_VIT_ATTN=sdpa).
+VIT_ATTN_IMPL = os.environ.get("MDT_VIT_ATTN", "mdt")
+
+
+def _mdt_vit_attention(module, query, key, value, attention_mask, scaling=None, dropout: float = 0.0, **kwargs):
+    """Hugging Face attention-interface function (``ALL_ATTENTION_FUNCTIONS``): ``query / key / value`` are ``[B, H, T, d]``.
+
+    bf16 CUDA tensors with d = 64 and no mask (every ViT block of mDT: 197 patches [+ 4 bottleneck tokens],
+    multi_graphormer_fusion_layer.py:73-100) run on ``mdt_biased_attn_fwd/bwd`` (no bias, in-kernel dropout); anything else
+    (the fp32 parity configurations) takes Hugging Face's own SDPA function, as the reference does."""
+    if (query.is_cuda and query.dtype == torch.bfloat16 and query.shape[-1] == 64 and attention_mask is None
+            and VIT_ATTN_IMPL == "mdt"):
+        scale = query.shape[-1] ** -0.5 if scaling is None else scaling
+        out = ops.biased_attention((query * scale).transpose(1, 2), key.transpose(1, 2), value.transpose(1, 2),
+                                   dropout_p=float(dropout))
+        return out, None
+    from transformers.modeling_utils import ALL_ATTENTION_FUNCTIONS
+
+    return ALL_ATTENTION_FUNCTIONS["sdpa"](module, query, key, value, attention_mask, scaling=scaling, dropout=dropout, **kwargs)
+
+
+def use_mdt_attention(module: nn.Module) -> nn.Module:
+    """Route the self-attention of every Hugging Face block below ``module`` through ``_mdt_vit_attention``."""
+    from transformers.modeling_utils import ALL_ATTENTION_FUNCTIONS
+
+    if "mdt_b200" not in ALL_ATTENTION_FUNCTIONS.valid_keys():
+        ALL_ATTENTION_FUNCTIONS.register("mdt_b200", _mdt_vit_attention)
+    for m in module.modules():
+        cfg = getattr(m, "config", None)
+        if cfg is not None and hasattr(cfg, "_attn_implementation") and cfg._attn_implementation in ("sdpa", "eager", None):
+            cfg._attn_implementation = "mdt_b200"
+    return module
+
+
 def use_fused_layer_norms(module: nn.Module) -> nn.Module:
     """Re-class every plain ``nn.LayerNorm`` below ``module`` (the ViT blocks are pre-LN: no residual to fuse)."""
     for m in module.modules():
@@ -192,7 +227,7 @@ class GraphFusionLayer(nn.Module):
     def __init__(self, bert_layer, vit_layer, num_bottle_neck_tokens: int, use_projection: bool = False) -> None:
         super().__init__()
         self.bert_encoder = bert_layer
-        self.vit_encoder = use_fused_layer_norms(vit_layer)
+        self.vit_encoder = use_mdt_attention(use_fused_layer_norms(vit_layer))
         self.gradient_checkpointing = False
         self.num_bottle_neck_tokens = num_bottle_neck_tokens
         if use_projection:  # constructed, never applied (multi_graphormer_fusion_layer.py:22-27)

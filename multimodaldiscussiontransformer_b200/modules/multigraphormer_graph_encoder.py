@@ -17,7 +17,8 @@ from .. import ops
 from ._fairseq_compat import FairseqDropout, LayerNorm
 from .graphormer_graph_encoder_layer import GraphEncoderStack
 from .graphormer_layers import GraphAttnBias, GraphNodeFeature
-from .multi_graphormer_fusion_layer import GraphFusionStack, TextPack, image_rows, packed_bert_layer, use_fused_layer_norms
+from .multi_graphormer_fusion_layer import (GraphFusionStack, TextPack, image_rows, packed_bert_layer, use_fused_layer_norms,
+                                            use_mdt_attention)
 from .multihead_attention import MultiheadAttention
 
 logger = logging.getLogger(__name__)
@@ -94,6 +95,7 @@ class MultiGraphormerGraphEncoder(nn.Module):
          self.node_classifier, self.text_dropout) = self.build_vit_bert_encoders(
             num_fusion_layers + 1, attention_dropout, activation_dropout, bert_config, vit_config)
         use_fused_layer_norms(self.vit_model)  # the trunk ViT blocks' LayerNorms on csrc/layernorm.cu as well
+        use_mdt_attention(self.vit_model)      # ... and their self-attention on the tcgen05 kernels
         self.fusion_layers = nn.ModuleList([
             GraphFusionStack(t, v, num_bottle_neck, use_projection=True)
             for t, v in zip(_chunks(list(text_other_layers), num_fusion_stack), _chunks(list(vit_other_layers), num_fusion_stack))])
