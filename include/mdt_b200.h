@@ -135,7 +135,10 @@ int mdt_attn_bias_bwd(const void *grad_out, const int32_t *spatial_pos, int B, i
  * backward: grad_out like out; dq/dk/dv like q/k/v with their own strides (dq must be
  *   zero-filled f32 scratch `dq_accum` [B,H,T,64] -- it is reduced across key tiles -- and is
  *   converted into dq); grad_bias [B,H,T,T] (`bias_dtype`) or NULL; grad_lut [H,256] f32
- *   accumulated or NULL.
+ *   accumulated or NULL.  code_t [B,T,code_pitch] (optional, backward only) is the transpose of code inside each
+ *   graph, code_t[b][k][q] = code[b][q][k] (columns q >= T: MDT_CODE_MASKED); build it once per batch -- with it the
+ *   backward runs its warp-specialised kernel (a thread reads the codes of one key against 64 queries as 4 vector
+ *   loads); without it (NULL) the byte-gather kernel runs.  delta [B,H,T] f32 is scratch (may stay untouched).
  * ------------------------------------------------------------------------------------ */
 typedef struct mdt_attn_dims {
     int32_t B, H, T;
@@ -159,8 +162,8 @@ int mdt_debug_attn_trace(unsigned long long *dev_buffer);
 
 int mdt_biased_attn_bwd(const void *q, const void *k, const void *v, const void *out, const void *grad_out,
                         const float *lse, const mdt_attn_dims *dims, const void *bias, int bias_dtype,
-                        const uint8_t *code, int code_pitch, const float *lut, const uint8_t *key_pad,
-                        void *dq, void *dk, void *dv, const mdt_attn_dims *grad_dims, float *dq_accum,
+                        const uint8_t *code, const uint8_t *code_t, int code_pitch, const float *lut,
+                        const uint8_t *key_pad, void *dq, void *dk, void *dv, const mdt_attn_dims *grad_dims, float *dq_accum,
                         float *delta, void *grad_bias, float *grad_lut, float dropout_p, uint64_t dropout_seed,
                         mdt_stream_t stream);
 

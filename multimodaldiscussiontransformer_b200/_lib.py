@@ -45,7 +45,7 @@ SIGNATURES = {
                                     c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_uint64, c_void_p]),
     "mdt_debug_attn_trace": (c_int, [c_void_p]),
     "mdt_biased_attn_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, POINTER(AttnDims),
-                                    c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                    c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                     POINTER(AttnDims), c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_uint64, c_void_p]),
     "mdt_varlen_attn_plan_words": (c_int64, [c_int, c_int]),
     "mdt_varlen_attn_plan": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),

@@ -15,6 +15,8 @@
 //     dQ_i is reduced across key tiles with fp32 vector atomics into dq_accum (attn_dq_convert_kernel
 //     turns it into bf16).  d-bias is either stored ([B,H,T,T], coalesced along keys) or binned by
 //     bias code into per-thread shared-memory bins (conflict free, no atomics) -> grad_lut[h][code].
+#include <stdlib.h>
+
 #include "attn_common.cuh"
 
 namespace mdt {
@@ -511,8 +513,8 @@ using namespace mdt::attn;
 
 extern "C" int mdt_biased_attn_bwd(const void *q, const void *k, const void *v, const void *out, const void *grad_out,
                                    const float *lse, const mdt_attn_dims *d, const void *bias, int bias_dtype,
-                                   const uint8_t *code, int code_pitch, const float *lut, const uint8_t *key_pad, void *dq,
-                                   void *dk, void *dv, const mdt_attn_dims *g, float *dq_accum, float *delta,
+                                   const uint8_t *code, const uint8_t *code_t, int code_pitch, const float *lut,
+                                   const uint8_t *key_pad, void *dq, void *dk, void *dv, const mdt_attn_dims *g, float *dq_accum, float *delta,
                                    void *grad_bias, float *grad_lut, float dropout_p, uint64_t dropout_seed, mdt_stream_t stream) {
     if (int rc = require_sm100()) return rc;
     if (int rc = check_dims(d, "mdt_biased_attn_bwd")) return rc;
@@ -528,6 +530,8 @@ extern "C" int mdt_biased_attn_bwd(const void *q, const void *k, const void *v, 
     if (code) {
         MDT_REQUIRE(lut != nullptr, "mdt_biased_attn_bwd: code needs lut");
         MDT_REQUIRE(code_pitch >= d->T, "mdt_biased_attn_bwd: code_pitch must be >= T");
+        MDT_REQUIRE(code_t == nullptr || (code_pitch % 16 == 0 && ((uintptr_t)code_t & 15) == 0),
+                    "mdt_biased_attn_bwd: code_t needs a 16-byte aligned base and a pitch that is a multiple of 16");
     }
     const int64_t strides[] = {d->o_stride_b, d->o_stride_t, d->o_stride_h, g->o_stride_b, g->o_stride_t, g->o_stride_h,
                                g->q_stride_b, g->q_stride_t, g->q_stride_h, g->k_stride_b, g->k_stride_t, g->k_stride_h,
@@ -538,7 +542,12 @@ extern "C" int mdt_biased_attn_bwd(const void *q, const void *k, const void *v, 
     cudaStream_t st = as_stream(stream);
     const int B = d->B, H = d->H, T = d->T;
 
-    {  // delta = rowsum(dO * O)
+    const int mode = bias_mode(bias, bias_dtype, code);
+    const int Tmain = tail_split(T, mode == kBiasCode || mode == kBiasNone);
+    // code / no bias: warp-specialised kernel (attn_bwd2.cu); it computes delta itself unless the tail-key kernel needs the buffer
+    static const bool use_bwd2 = []() { const char *e = getenv("MDT_ATTN_BWD"); return !(e && e[0] == '1'); }();
+    const bool bwd2 = use_bwd2 && (mode == kBiasNone || (mode == kBiasCode && code_t != nullptr));
+    if (!bwd2 || Tmain < T) {  // delta = rowsum(dO * O)
         const int64_t rows = (int64_t)B * H * T;
         const int threads = 256, rows_per_block = threads / 8;
         attn_delta_kernel<<<(unsigned)((rows + rows_per_block - 1) / rows_per_block), threads, 0, st>>>(
@@ -560,13 +569,25 @@ extern "C" int mdt_biased_attn_bwd(const void *q, const void *k, const void *v, 
     a.dv_sb = g->v_stride_b, a.dv_st = g->v_stride_t, a.dv_sh = g->v_stride_h;
     a.grad_bias = grad_bias, a.grad_lut = grad_lut;
     a.drop = make_drop(dropout_p, dropout_seed);
-    const int mode = bias_mode(bias, bias_dtype, code);
-    a.Tmain = tail_split(T, mode == kBiasCode || mode == kBiasNone);
-    CUtensorMap mc = mq;  // only read by the code mode
+    a.Tmain = Tmain;
+    CUtensorMap mc = mq;  // only read by the code mode: [query][key] tiles of code, or [key][query] tiles of code_t (bwd2)
     if (code)
-        if (int rc2 = make_tensor_map_u8_2d(&mc, code, (uint64_t)code_pitch, (uint64_t)B * T, (uint64_t)code_pitch, kTile)) return rc2;
+        if (int rc2 = make_tensor_map_u8_2d(&mc, bwd2 ? code_t : code, (uint64_t)code_pitch, (uint64_t)B * T, (uint64_t)code_pitch, kTile)) return rc2;
     int rc;
-    switch (bias_mode(bias, bias_dtype, code)) {
+    if (bwd2) {
+        Bwd2Args a2{};
+        a2.B = B, a2.H = H, a2.T = T, a2.Tmain = Tmain;
+        a2.key_pad = key_pad, a2.lut = lut, a2.lse = lse;
+        a2.delta = Tmain < T ? delta : nullptr;
+        a2.out = reinterpret_cast<const __nv_bfloat16 *>(out), a2.dout = reinterpret_cast<const __nv_bfloat16 *>(grad_out);
+        a2.o_sb = d->o_stride_b, a2.o_st = d->o_stride_t, a2.o_sh = d->o_stride_h;
+        a2.g_sb = g->o_stride_b, a2.g_st = g->o_stride_t, a2.g_sh = g->o_stride_h;
+        a2.dq_accum = dq_accum, a2.dk = a.dk, a2.dv = a.dv;
+        a2.dk_sb = a.dk_sb, a2.dk_st = a.dk_st, a2.dk_sh = a.dk_sh, a2.dv_sb = a.dv_sb, a2.dv_st = a.dv_st, a2.dv_sh = a.dv_sh;
+        a2.grad_lut = grad_lut, a2.drop = a.drop;
+        rc = launch_bwd2(mq, mk, mv, mdo, mc, a2, code != nullptr, st);
+    } else
+    switch (mode) {
         case kBiasNone: rc = launch_bwd<kBiasNone>(mq, mk, mv, mdo, mc, a, st); break;
         case kBiasF32: rc = launch_bwd<kBiasF32>(mq, mk, mv, mdo, mc, a, st); break;
         case kBiasBF16: rc = launch_bwd<kBiasBF16>(mq, mk, mv, mdo, mc, a, st); break;

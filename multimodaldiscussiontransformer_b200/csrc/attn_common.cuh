@@ -103,6 +103,25 @@ int launch_fwd3(const CUtensorMap &mq, const CUtensorMap &mk, const CUtensorMap 
                 cudaStream_t st);
 
 
+// warp-specialised backward for bias from codes / no bias (attn_bwd2.cu)
+struct Bwd2Args {
+    int B, H, T, Tmain;
+    const uint8_t *key_pad;
+    const float *lut;
+    const float *lse;
+    const float *delta;  // precomputed rowsum(dO * O), or null: computed here from out / dout
+    const __nv_bfloat16 *out, *dout;
+    int64_t o_sb, o_st, o_sh, g_sb, g_st, g_sh;
+    float *dq_accum;
+    __nv_bfloat16 *dk, *dv;
+    int64_t dk_sb, dk_st, dk_sh, dv_sb, dv_st, dv_sh;
+    float *grad_lut;
+    DropArgs drop;
+};
+
+int launch_bwd2(const CUtensorMap &mq, const CUtensorMap &mk, const CUtensorMap &mv, const CUtensorMap &mdo, const CUtensorMap &mc,
+                const Bwd2Args &a, bool has_code, cudaStream_t st);
+
 // tail keys of T = 128 k + r in the backward (attn_tail.cu): keys [Tmain, T) on CUDA cores
 constexpr int kTailMax = 8;
 inline int tail_split(int T, bool eligible) {  // -> Tmain

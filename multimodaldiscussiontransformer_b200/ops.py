@@ -227,6 +227,21 @@ def _check_bthd(name: str, t: torch.Tensor) -> torch.Tensor:
     return t if ok else t.contiguous()
 
 
+def transposed_code(code: torch.Tensor) -> torch.Tensor:
+    """``code_t[b, k, q] = code[b, q, k]`` (columns ``q >= T``: 255) for the backward's vector code loads.  Built once
+    per ``code`` tensor -- every layer and head of a batch shares the same codes -- and cached on the tensor object."""
+    ct = getattr(code, "_mdt_code_t", None)
+    if ct is None:
+        B, T, pitch = code.shape
+        ct = torch.full_like(code, _lib.CODE_MASKED)
+        ct[:, :, :T] = code[:, :, :T].transpose(1, 2)
+        try:
+            code._mdt_code_t = ct
+        except Exception:  # a tensor subclass that refuses attributes: recompute next time
+            pass
+    return ct
+
+
 def _empty_like_layout(q: torch.Tensor) -> torch.Tensor:
     """Output buffer [B,T,H,64] whose memory order follows q's (t-major for the encoder's [T,B,C] activations)."""
     B, T, H, D = q.shape
@@ -289,8 +304,8 @@ class _BiasedAttention(torch.autograd.Function):
         with torch.cuda.device(q.device), _timed("bwd", B, H, T):
             _lib.check(lib.mdt_biased_attn_bwd(
                 _lib.ptr(q), _lib.ptr(k), _lib.ptr(v), _lib.ptr(out), _lib.ptr(go), _lib.ptr(lse), ctypes.byref(dims),
-                _lib.ptr(bias), _lib.dtype_code(bias.dtype) if bias is not None else 0, _lib.ptr(code), ctx.pitch,
-                _lib.ptr(lut), _lib.ptr(key_pad), _lib.ptr(dq), _lib.ptr(dk), _lib.ptr(dv), ctypes.byref(gdims),
+                _lib.ptr(bias), _lib.dtype_code(bias.dtype) if bias is not None else 0, _lib.ptr(code),
+                _lib.ptr(transposed_code(code)) if code is not None else None, ctx.pitch, _lib.ptr(lut), _lib.ptr(key_pad), _lib.ptr(dq), _lib.ptr(dk), _lib.ptr(dv), ctypes.byref(gdims),
                 _lib.ptr(dq_accum), _lib.ptr(delta), _lib.ptr(g_bias), _lib.ptr(g_lut), ctx.drop[0], ctx.drop[1],
                 _lib.stream()), "mdt_biased_attn_bwd")
         if bias is None and T > 128 and 1 <= T % 128 <= 8:  # + attn_bwd_tail_k_kernel (csrc/attn_tail.cu), for the launch count
