@@ -250,9 +250,10 @@ int mdt_dropout_add_ln_bwd(const void *dy, const void *z, const float *mean, con
  *   d1[128,128] = a[128,64] * b[128,64]^T          (A and B K-major, both via TMA)
  *   d2[128,64]  = p[128,128] * v[128,64]           (A K-major written by threads, B MN-major)
  *   d3[128,64]  = at[128(K),128(M)]^T * bk[64(N),128(K)]^T   (A MN-major, B K-major)
- * d1..d3 are f32 device buffers. */
+ *   d4[128,64]  = p[128,128] * v[128,64]           (A read from TENSOR MEMORY, written there by tcgen05.st; B MN-major)
+ * d1..d4 are f32 device buffers. */
 int mdt_umma_selftest(const void *a, const void *b, const void *p, const void *v, const void *at, const void *bk,
-                      float *d1, float *d2, float *d3, mdt_stream_t stream);
+                      float *d1, float *d2, float *d3, float *d4, mdt_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -64,7 +64,7 @@ SIGNATURES = {
                                        c_int, c_float, c_uint64, c_float, c_void_p]),
     "mdt_dropout_add_ln_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                        c_int64, c_int, c_float, c_uint64, c_void_p]),
-    "mdt_umma_selftest": (c_int, [c_void_p] * 10),
+    "mdt_umma_selftest": (c_int, [c_void_p] * 11),
 }
 
 

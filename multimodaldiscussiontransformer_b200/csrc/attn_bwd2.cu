@@ -21,7 +21,10 @@
 //               dK += dS^T Q_i (128x64x128)
 //   warp  17    TMA producer (one lane): K, V once; Q_i, dO_i and the TRANSPOSED byte-code tile [key][query] double-buffered
 //   warps 18-19 idle (register donors: setmaxnreg works per warpgroup)
-// TMEM columns: S^T [0,128) dP^T [128,256) dV [256,320) dK [320,384) dQ [384,448).
+// TMEM columns: S^T [0,128) dP^T [128,256) dV [256,320) dK [320,384) dQ [384,448) P^T (bf16 pairs) [448,512).
+// P^T never touches shared memory: it is the A operand of dV += P^T dO_i read from tensor memory (lane = key row,
+// 32-bit column j = queries 2j, 2j+1), written there by the softmax threads with tcgen05.st.  dS^T goes to shared memory
+// (dQ_i = dS K reads it MN-major, dK += dS^T Q_i K-major, the LUT-gradient warps re-read it).
 // The code tile is read from code_t[b][k][q] = code[b][q][k] (one transpose per batch, shared by every layer and head):
 // a thread needs the codes of ONE key against 64 queries, which is a row of the transposed tile (4 x 16-byte loads)
 // instead of 64 byte loads strided by the row pitch.
@@ -33,7 +36,7 @@ using namespace sm100;
 
 constexpr int kB2Threads = 640;
 constexpr int kB2Bins = 24;  // bias codes 0..22 have their own bin, MDT_CODE_VIRTUAL uses bin 23 (include/mdt_b200.h)
-constexpr int kB2Tiles = 16384 * 2 /*K,V*/ + 2 * 16384 /*Q x2*/ + 2 * 16384 /*dO x2*/ + 32768 /*P^T*/ + 32768 /*dS^T*/;
+constexpr int kB2Tiles = 16384 * 2 /*K,V*/ + 2 * 16384 /*Q x2*/ + 2 * 16384 /*dO x2*/ + 32768 /*dS^T*/;
 constexpr int kB2CodeBytes = 2 * 16384;
 constexpr int kB2BinsBytes = 2 * kB2Bins * 128 * 4;
 
@@ -56,7 +59,7 @@ __global__ void __launch_bounds__(kB2Threads, 1)
                      const __grid_constant__ CUtensorMap mv, const __grid_constant__ CUtensorMap mdo,
                      const __grid_constant__ CUtensorMap mc, const Bwd2Args a) {
     extern __shared__ __align__(1024) uint8_t smem[];
-    uint8_t *sK = smem, *sV = smem + 16384, *sQ = smem + 32768, *sdO = smem + 65536, *sPt = smem + 98304, *sdSt = smem + 131072;
+    uint8_t *sK = smem, *sV = smem + 16384, *sQ = smem + 32768, *sdO = smem + 65536, *sdSt = smem + 98304;
     uint8_t *sCode = smem + kB2Tiles;  // 2 x [128 keys][128 queries] bytes, 128-byte swizzle
     const bool want_glut = HAS_CODE && a.grad_lut != nullptr;
     float *bins = reinterpret_cast<float *>(smem + kB2Tiles + (HAS_CODE ? kB2CodeBytes : 0));  // [2][kB2Bins][128]
@@ -123,7 +126,7 @@ __global__ void __launch_bounds__(kB2Threads, 1)
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = ctl.tmem_base;
-    constexpr uint32_t cS = 0, cDP = 128, cDV = 256, cDK = 320, cDQ = 384;
+    constexpr uint32_t cS = 0, cDP = 128, cDV = 256, cDK = 320, cDQ = 384, cPT = 448;
 
     if (warp >= 16) {
         // ------------------------------------------------------------------ MMA issuer / TMA producer / idle
@@ -147,7 +150,7 @@ __global__ void __launch_bounds__(kB2Threads, 1)
             const uint32_t idesc_s = idesc_bf16(128, 128, 0, 0);
             const uint32_t idesc_kv = idesc_bf16(128, 64, 0, 1);
             const uint32_t idesc_dq = idesc_bf16(128, 64, 1, 1);
-            const uint32_t ak = smem_u32(sK), av = smem_u32(sV), ap = smem_u32(sPt), ad = smem_u32(sdSt);
+            const uint32_t ak = smem_u32(sK), av = smem_u32(sV), ad = smem_u32(sdSt);
             auto issue_s_dp = [&](int i) {
                 const uint32_t bq = smem_u32(sQ + (i & 1) * 16384), bo = smem_u32(sdO + (i & 1) * 16384);
                 tc_fence_after();
@@ -179,9 +182,8 @@ __global__ void __launch_bounds__(kB2Threads, 1)
                               idesc_dq, k > 0);
                 umma_commit(&ctl.dq_full);
 #pragma unroll
-                for (int k = 0; k < 8; ++k)  // dV += P^T dO_i
-                    umma_bf16(tmem + cDV, smem_desc_sw128(ap + (k >> 2) * 16384 + (k & 3) * 32, 16, 1024),
-                              smem_desc_sw128(bo + k * 2048, 8192, 1024), idesc_kv, (k > 0) ? 1u : acc);
+                for (int k = 0; k < 8; ++k)  // dV += P^T dO_i   (A = P^T from tensor memory: 8 columns per 16 queries)
+                    umma_bf16_ts(tmem + cDV, tmem + cPT + k * 8, smem_desc_sw128(bo + k * 2048, 8192, 1024), idesc_kv, (k > 0) ? 1u : acc);
 #pragma unroll
                 for (int k = 0; k < 8; ++k)  // dK += dS^T Q_i
                     umma_bf16(tmem + cDK, smem_desc_sw128(ad + (k >> 2) * 16384 + (k & 3) * 32, 16, 1024),
@@ -375,29 +377,31 @@ __global__ void __launch_bounds__(kB2Threads, 1)
                 mbar_wait(&ctl.pds_free, (i - 1) & 1);                      // the MMAs of tile i-1 have read the P^T / dS^T tiles
                 if (want_glut) mbar_wait(&ctl.bin_free[(i - 1) & 1], ((i - 1) >> 1) & 1);  // ... and so have the bin warps
             }
-            if (!(live && key_ok)) {   // masked key, or query columns past T: P^T = dS^T = 0
+            {
+                // masked key, or query columns past T: P^T = dS^T = 0.  The TMEM stores are warp-collective, so every lane
+                // executes them and the per-lane case is a select, not a branch.
+                const bool on = live && key_ok;
+                const uint32_t tP = lane_base + cPT + half * 32;
+#pragma unroll
+                for (int hh = 0; hh < 2; ++hh) {
+                    uint32_t pw[16];
+#pragma unroll
+                    for (int u = 0; u < 16; ++u) pw[u] = on ? pack_bf16x2(st[hh * 32 + 2 * u], st[hh * 32 + 2 * u + 1]) : 0u;
+                    tmem_st_32x16(tP + hh * 16, pw);
+                }
 #pragma unroll
                 for (int u = 0; u < 8; ++u) {
-                    const uint32_t off = half * 16384 + sw128_offset(r, u);
-                    *reinterpret_cast<uint4 *>(sPt + off) = make_uint4(0, 0, 0, 0);
-                    *reinterpret_cast<uint4 *>(sdSt + off) = make_uint4(0, 0, 0, 0);
+                    uint4 vd = make_uint4(0, 0, 0, 0);
+                    if (on) {
+                        vd.x = pack_bf16x2(dp[u * 8 + 0], dp[u * 8 + 1]);
+                        vd.y = pack_bf16x2(dp[u * 8 + 2], dp[u * 8 + 3]);
+                        vd.z = pack_bf16x2(dp[u * 8 + 4], dp[u * 8 + 5]);
+                        vd.w = pack_bf16x2(dp[u * 8 + 6], dp[u * 8 + 7]);
+                    }
+                    *reinterpret_cast<uint4 *>(sdSt + half * 16384 + sw128_offset(r, u)) = vd;
                 }
-            } else {
-#pragma unroll
-                for (int u = 0; u < 8; ++u) {
-                    uint4 vp, vd;
-                    vp.x = pack_bf16x2(st[u * 8 + 0], st[u * 8 + 1]);
-                    vp.y = pack_bf16x2(st[u * 8 + 2], st[u * 8 + 3]);
-                    vp.z = pack_bf16x2(st[u * 8 + 4], st[u * 8 + 5]);
-                    vp.w = pack_bf16x2(st[u * 8 + 6], st[u * 8 + 7]);
-                    vd.x = pack_bf16x2(dp[u * 8 + 0], dp[u * 8 + 1]);
-                    vd.y = pack_bf16x2(dp[u * 8 + 2], dp[u * 8 + 3]);
-                    vd.z = pack_bf16x2(dp[u * 8 + 4], dp[u * 8 + 5]);
-                    vd.w = pack_bf16x2(dp[u * 8 + 6], dp[u * 8 + 7]);
-                    const uint32_t off = half * 16384 + sw128_offset(r, u);
-                    *reinterpret_cast<uint4 *>(sPt + off) = vp;
-                    *reinterpret_cast<uint4 *>(sdSt + off) = vd;
-                }
+                tmem_wait_st();
+                tc_fence_before();
             }
             fence_proxy_async();
             mbar_arrive(&ctl.pds_full);

@@ -15,8 +15,12 @@
 // run straight across item boundaries, so the loads, the first S MMA and the prologue of item n+1 overlap the
 // softmax and the epilogue of item n.  S_t(g+1) is issued as soon as the softmax warpgroup has pulled S_t(g)
 // into registers, so it executes under softmax(g).
-// TMEM columns: S0 [0,128) S1 [128,256) O0 [256,320) O1 [320,384).
-// Shared memory (all dynamic, 1024-byte aligned): Q0 Q1 | 2 stages x (K, V, code0, code1) | P0 P1 | control.
+// TMEM columns: S0 [0,128) S1 [128,256) O0 [256,320) O1 [320,384) P0 [384,448) P1 [448,512).
+// P never touches shared memory: the softmax threads pack their probabilities to bf16 pairs and store them into tensor
+// memory (tcgen05.st; lane = query row, 32-bit column j = keys 2j, 2j+1), and O_t += P_t V reads its A operand from there
+// (tcgen05.mma with A in TMEM).  That removes 32 KB of shared-memory stores and 32 KB of operand fetches per 128x128 tile
+// -- a third of the kernel's shared-memory traffic, which (not the tensor pipe) bounds it at head dim 64.
+// Shared memory (all dynamic, 1024-byte aligned): Q0 Q1 | 2 stages x (K, V, code0, code1) | control.
 #include "attn_common.cuh"
 
 namespace mdt {
@@ -26,7 +30,7 @@ using namespace sm100;
 constexpr int kF3Threads = 640;
 constexpr int kF3SoftmaxWarps = 16;
 constexpr int kF3Stage = 4 * 16384;  // K, V, code0, code1
-constexpr int kF3Tiles = 2 * 16384 + 2 * kF3Stage + 2 * 32768;
+constexpr int kF3Tiles = 2 * 16384 + 2 * kF3Stage;
 constexpr float kF3Rescale = 8.0f;   // log2 units: P may reach 2^8 before O is rescaled
 constexpr int kF3MaskWords = kFwd3MaxT / 32;
 
@@ -40,6 +44,8 @@ struct F3Ctrl {
     uint32_t tmem_base;
     int nkv[2];
     uint32_t kmask[2][kF3MaskWords];  // bit set = key masked (padding or >= T)
+    float xmax[2][2][2][128];         // [k-step parity][query tile][column half][row]: row maximum exchange between the halves
+    float xsum[2][2][2][128];         // [item parity][query tile][column half][row]: the row sums, once per item
 };
 constexpr int kF3Smem = kF3Tiles + (int)sizeof(F3Ctrl);
 
@@ -64,14 +70,15 @@ __device__ __forceinline__ F3Item f3_item(int item, int nqp, int H) {
     return it;
 }
 
-template <bool HAS_CODE>
+// HAS_DROP is a template parameter: a run-time (uniform) test per element pair would cut the unrolled softmax loop into
+// basic blocks and keep the exponentials of different elements from being interleaved.
+template <bool HAS_CODE, bool HAS_DROP>
 __global__ void __launch_bounds__(kF3Threads, 1)
     attn_fwd3_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__ CUtensorMap mk,
                      const __grid_constant__ CUtensorMap mv, const __grid_constant__ CUtensorMap mc, const Fwd2Args a) {
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t *sQ = smem;                       // 2 x 16 KB
     uint8_t *sStage = smem + 2 * 16384;       // 2 x 64 KB
-    uint8_t *sP = sStage + 2 * kF3Stage;      // 2 x 32 KB
     F3Ctrl &ctl = *reinterpret_cast<F3Ctrl *>(smem + kF3Tiles);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -117,7 +124,7 @@ __global__ void __launch_bounds__(kF3Threads, 1)
 
     if (warp >= kF3SoftmaxWarps) {
         // ------------------------------------------------------------------ producer / MMA / aux warpgroup
-        reg_dealloc<40>();
+        reg_dealloc<64>();  // 640 x 96 registers at launch = 512 x 104 + 128 x 64
         if (warp == kF3SoftmaxWarps + 2) {
             // ---- aux: key-mask bitmap, live key tiles and LUT of item n into buffer n & 1, one item ahead
             int n = 0;
@@ -258,11 +265,11 @@ __global__ void __launch_bounds__(kF3Threads, 1)
                             for (int t = 0; t < 2; ++t) {
                                 if (!pv_done[t] && mbar_try_wait(&ctl.p_full[t], g & 1)) {
                                     tc_fence_after();
-                                    const uint32_t ap = smem_u32(sP + t * 32768), bv = smem_u32(sStage + s * kF3Stage + 16384);
+                                    const uint32_t bv = smem_u32(sStage + s * kF3Stage + 16384);
 #pragma unroll
-                                    for (int k = 0; k < 8; ++k)
-                                        umma_bf16(tmem + 256 + t * 64, smem_desc_sw128(ap + (k >> 2) * 16384 + (k & 3) * 32, 16, 1024),
-                                                  smem_desc_sw128(bv + k * 2048, 8192, 1024), idesc_o, (j > 0 || k > 0) ? 1u : 0u);
+                                    for (int k = 0; k < 8; ++k)  // A = P_t from tensor memory: 8 columns per 16 keys
+                                        umma_bf16_ts(tmem + 256 + t * 64, tmem + 384 + t * 64 + k * 8,
+                                                     smem_desc_sw128(bv + k * 2048, 8192, 1024), idesc_o, (j > 0 || k > 0) ? 1u : 0u);
                                     umma_commit(&ctl.o_done[t]);
                                     if (j == 0 && t == 0) f3_trace(a, 2 + 12 * n + 9);
                                     pv_done[t] = true;
@@ -287,8 +294,7 @@ __global__ void __launch_bounds__(kF3Threads, 1)
         const int r = tid & 127;                       // row inside the tile == TMEM lane
         const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
         const uint32_t tS = lane_base + t * 128 + hf * 64, tO = lane_base + 256 + t * 64 + hf * 32;
-        const uint32_t myP = smem_u32(sP + t * 32768) + hf * 16384;   // this half = one 64-key K block of P_t
-        const uint32_t otherP = smem_u32(sP + t * 32768) + (hf ^ 1) * 16384;
+        const uint32_t tP = lane_base + 384 + t * 64 + hf * 32;       // this half = keys [64 hf, 64 hf + 64) of P_t, bf16 pairs
         const uint32_t bar_id = 1 + t;                 // named barrier of the two warpgroups sharing tile t
         int n = 0;
         uint32_t g = 0;
@@ -372,17 +378,14 @@ __global__ void __launch_bounds__(kF3Threads, 1)
                 float mx = fmaxf(mx0, mx1);
                 if (tid == 0 && j == 0) f3_trace(a, 2 + 12 * n + 2);
                 {
-                    const uint32_t mine = crow + sw128_offset(r, hf * 4), other = crow + sw128_offset(r, (hf ^ 1) * 4);
+                    const uint32_t mine = smem_u32(&ctl.xmax[g & 1][t][hf][r]), other = smem_u32(&ctl.xmax[g & 1][t][hf ^ 1][r]);
                     asm volatile("st.shared.f32 [%0], %1;" ::"r"(mine), "f"(mx) : "memory");
                     asm volatile("bar.sync %0, 256;" ::"r"(bar_id) : "memory");
                     float omx;
                     asm volatile("ld.shared.f32 %0, [%1];" : "=f"(omx) : "r"(other) : "memory");
                     mx = fmaxf(mx, omx);
                 }
-                if (HAS_CODE) {
-                    fence_proxy_async();                  // the published word precedes the next TMA write of this slot
-                    mbar_arrive(&ctl.c_empty[s]);
-                }
+                if (HAS_CODE) mbar_arrive(&ctl.c_empty[s]);  // the code tile has been read (pass 1)
                 float alpha = 1.f;
                 bool grow = false;
                 if (warp_live) {
@@ -409,12 +412,13 @@ __global__ void __launch_bounds__(kF3Threads, 1)
                         tmem_wait_st();
                     }
                 }
-                // ---- pass 2: p = 2^(x - m), row sum, bf16 P tile (128-byte swizzle, K-major A operand of P V)
+                // ---- pass 2: p = 2^(x - m), row sum, bf16 pairs -> tensor memory (A operand of P V: lane = row, column = key pair)
                 if (warp_live) {
                     const float nm = (m_used == neg_inf()) ? 0.f : -m_used;
                     float sum0 = 0.f, sum1 = 0.f;
 #pragma unroll
                     for (int c = 0; c < 2; ++c) {
+                        uint32_t pw[16];  // 32 keys of this row as bf16 pairs
                         if (kmask[c] != 0xffffffffu) {
 #pragma unroll
                             for (int ch = 4 * c; ch < 4 * c + 4; ++ch) {
@@ -425,42 +429,39 @@ __global__ void __launch_bounds__(kF3Threads, 1)
                                     x[i] = ex2(x[i]);
                                     x[i + 1] = ex2(x[i + 1]);
                                     fadd2(sum0, sum1, sum0, sum1, x[i], x[i + 1]);   // the row sum is of the undropped p
-                                    if (a.drop.thr16) {  // dropout on P (multihead_attention.py:196): keys k, k + 1 share one hash
+                                    if (HAS_DROP) {  // dropout on P (multihead_attention.py:196): keys k, k + 1 share one hash
                                         const uint32_t hp = drop_hash(salt, drop_row + (uint32_t)(j * kTile + hf * 64 + ch * 8 + i));
                                         x[i] = (hp >> 16) >= a.drop.thr16 ? x[i] * a.drop.scale : 0.f;
                                         x[i + 1] = (hp & 0xffffu) >= a.drop.thr16 ? x[i + 1] * a.drop.scale : 0.f;
                                     }
+                                    pw[(ch - 4 * c) * 4 + (i >> 1)] = pack_bf16x2(x[i], x[i + 1]);
                                 }
-                                uint4 v;
-                                v.x = pack_bf16x2(x[0], x[1]);
-                                v.y = pack_bf16x2(x[2], x[3]);
-                                v.z = pack_bf16x2(x[4], x[5]);
-                                v.w = pack_bf16x2(x[6], x[7]);
-                                sts_u4(myP + sw128_offset(r, ch), v);
                             }
                         } else {
 #pragma unroll
-                            for (int ch = 4 * c; ch < 4 * c + 4; ++ch) sts_u4(myP + sw128_offset(r, ch), make_uint4(0, 0, 0, 0));
+                            for (int w = 0; w < 16; ++w) pw[w] = 0u;
                         }
+                        tmem_st_32x16(tP + c * 16, pw);
                     }
                     l += sum0 + sum1;
+                    tmem_wait_st();
                 }
-                fence_proxy_async();
                 tc_fence_before();
                 mbar_arrive(&ctl.p_full[t]);
                 if (tid == 0 && j == 0) f3_trace(a, 2 + 12 * n + 3);
             }
             mbar_arrive(&ctl.aux_empty[buf]);          // key mask and LUT of this item are no longer read
-            // ---- epilogue: O / l -> bf16, log-sum-exp.  P_t is free after the last P V: the halves add their row sums there.
+            // ---- epilogue: O / l -> bf16, log-sum-exp; the halves add their row sums
             mbar_wait(&ctl.o_done[t], (g - 1) & 1);
             if (tid == 0) f3_trace(a, 2 + 12 * n + 4);
             tc_fence_after();
             __syncwarp();
             {
-                asm volatile("st.shared.f32 [%0], %1;" ::"r"(myP + sw128_offset(r, 0)), "f"(l) : "memory");
+                const uint32_t mine = smem_u32(&ctl.xsum[n & 1][t][hf][r]), other = smem_u32(&ctl.xsum[n & 1][t][hf ^ 1][r]);
+                asm volatile("st.shared.f32 [%0], %1;" ::"r"(mine), "f"(l) : "memory");
                 asm volatile("bar.sync %0, 256;" ::"r"(bar_id) : "memory");
                 float ol;
-                asm volatile("ld.shared.f32 %0, [%1];" : "=f"(ol) : "r"(otherP + sw128_offset(r, 0)) : "memory");
+                asm volatile("ld.shared.f32 %0, [%1];" : "=f"(ol) : "r"(other) : "memory");
                 l += ol;
             }
             if (warp_live) {
@@ -494,17 +495,20 @@ __global__ void __launch_bounds__(kF3Threads, 1)
 
 int launch_fwd3(const CUtensorMap &mq, const CUtensorMap &mk, const CUtensorMap &mv, const CUtensorMap &mc, const Fwd2Args &a,
                 cudaStream_t st) {
-    if (a.has_code)  // per launch: the attribute is per device
-        MDT_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd3_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kF3Smem));
-    else
-        MDT_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd3_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kF3Smem));
+    const bool drop = a.drop.thr16 != 0;
+#define MDT_LAUNCH_F3(C, D)                                                                                               \
+    do {                                                                                                                  \
+        MDT_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd3_kernel<C, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, kF3Smem)); \
+        attn_fwd3_kernel<C, D><<<grid, kF3Threads, kF3Smem, st>>>(mq, mk, mv, mc, a);                                      \
+    } while (0)
     const int nqp = (a.Tmain + 2 * kTile - 1) / (2 * kTile);
     const long long n_items = (long long)a.B * a.H * nqp;
     const int grid = (int)(n_items < (long long)num_sms() ? n_items : (long long)num_sms());
-    if (a.has_code)
-        attn_fwd3_kernel<true><<<grid, kF3Threads, kF3Smem, st>>>(mq, mk, mv, mc, a);
-    else
-        attn_fwd3_kernel<false><<<grid, kF3Threads, kF3Smem, st>>>(mq, mk, mv, mc, a);
+    if (a.has_code && drop) MDT_LAUNCH_F3(true, true);
+    else if (a.has_code) MDT_LAUNCH_F3(true, false);
+    else if (drop) MDT_LAUNCH_F3(false, true);
+    else MDT_LAUNCH_F3(false, false);
+#undef MDT_LAUNCH_F3
     MDT_CHECK_CUDA(cudaGetLastError());
     return MDT_OK;
 }

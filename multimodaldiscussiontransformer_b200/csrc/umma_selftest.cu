@@ -12,7 +12,7 @@ __global__ void __launch_bounds__(128, 1)
     umma_selftest_kernel(const __grid_constant__ CUtensorMap ma, const __grid_constant__ CUtensorMap mb,
                          const __grid_constant__ CUtensorMap mv, const __grid_constant__ CUtensorMap mat,
                          const __grid_constant__ CUtensorMap mbk, const __nv_bfloat16 *__restrict__ p_g, float *d1,
-                         float *d2, float *d3) {
+                         float *d2, float *d3, float *d4) {
     extern __shared__ __align__(1024) uint8_t smem_dyn[];
     uint8_t *smem = reinterpret_cast<uint8_t *>(((uintptr_t)smem_dyn + 1023) & ~(uintptr_t)1023);
     __shared__ __align__(8) uint64_t bar_tma, bar_mma;
@@ -27,7 +27,7 @@ __global__ void __launch_bounds__(128, 1)
         fence_barrier_init();
     }
     if (warp == 0) {
-        tmem_alloc(&tmem_base_s, 256);
+        tmem_alloc(&tmem_base_s, 512);
         tmem_relinquish();
     }
     // P [128 x 128] row-major in global -> two K-major SW128 sub-tiles written by threads
@@ -41,6 +41,18 @@ __global__ void __launch_bounds__(128, 1)
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = tmem_base_s;
+    {   // P row `tid` -> TMEM columns 256..319 of lane `tid`: 32-bit column j holds elements 2j, 2j+1 (K order)
+        uint32_t w[64];
+        const uint32_t *src = reinterpret_cast<const uint32_t *>(p_g + tid * 128);
+        for (int j = 0; j < 64; ++j) w[j] = src[j];
+        const uint32_t lane_addr = tmem + ((uint32_t)(warp * 32) << 16);
+        tmem_st_32x32(lane_addr + 256, w);
+        tmem_st_32x32(lane_addr + 288, w + 32);
+        tmem_wait_st();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
 
     if (tid == 0) {
         mbar_expect_tx(&bar_tma, 16384 * 3 + 32768 + 16384);
@@ -59,6 +71,13 @@ __global__ void __launch_bounds__(128, 1)
             for (int k = 0; k < 4; ++k)
                 umma_bf16(tmem, smem_desc_sw128(smem_u32(sA) + k * 32, 16, 1024), smem_desc_sw128(smem_u32(sB) + k * 32, 16, 1024),
                           id, k > 0);
+        }
+        // test 4: D4[128,64] = P[128,128] * V[128,64] with A = P read from TENSOR MEMORY (bf16 pairs packed into 32-bit
+        // columns 256..319 of lane = row by the threads, tcgen05.st) -> cols 320..383
+        {
+            const uint32_t id = idesc_bf16(128, 64, 0, 1);
+            for (int k = 0; k < 8; ++k)
+                umma_bf16_ts(tmem + 320, tmem + 256 + k * 8, smem_desc_sw128(smem_u32(sV) + k * 2048, 8192, 1024), id, k > 0);
         }
         // test 2: D2[128,64] = P[128,128] * V[128,64]         (A K-major, B MN-major) -> cols 128..191
         {
@@ -97,9 +116,14 @@ __global__ void __launch_bounds__(128, 1)
         tmem_wait_ld();
         for (int j = 0; j < 32; ++j) d3[row * 64 + c * 32 + j] = __uint_as_float(r[j]);
     }
+    for (int c = 0; c < 2; ++c) {
+        tmem_ld_32x32(lane_base + 320 + c * 32, r);
+        tmem_wait_ld();
+        for (int j = 0; j < 32; ++j) d4[row * 64 + c * 32 + j] = __uint_as_float(r[j]);
+    }
     tc_fence_before();
     __syncthreads();
-    if (warp == 0) tmem_dealloc(tmem, 256);
+    if (warp == 0) tmem_dealloc(tmem, 512);
 }
 
 }  // namespace mdt
@@ -107,9 +131,9 @@ __global__ void __launch_bounds__(128, 1)
 using namespace mdt;
 
 extern "C" int mdt_umma_selftest(const void *a, const void *b, const void *p, const void *v, const void *at, const void *bk,
-                                 float *d1, float *d2, float *d3, mdt_stream_t stream) {
+                                 float *d1, float *d2, float *d3, float *d4, mdt_stream_t stream) {
     if (int rc = require_sm100()) return rc;
-    MDT_REQUIRE(a && b && p && v && at && bk && d1 && d2 && d3, "null pointer");
+    MDT_REQUIRE(a && b && p && v && at && bk && d1 && d2 && d3 && d4, "null pointer");
     CUtensorMap ma, mb, mv, mat, mbk;
     const uint32_t box64x128[2] = {64, 128}, box64x64[2] = {64, 64};
     {
@@ -128,7 +152,7 @@ extern "C" int mdt_umma_selftest(const void *a, const void *b, const void *p, co
     }
     const int smem = 131072 + 1024;
     MDT_CHECK_CUDA(cudaFuncSetAttribute(umma_selftest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    umma_selftest_kernel<<<1, 128, smem, as_stream(stream)>>>(ma, mb, mv, mat, mbk, (const __nv_bfloat16 *)p, d1, d2, d3);
+    umma_selftest_kernel<<<1, 128, smem, as_stream(stream)>>>(ma, mb, mv, mat, mbk, (const __nv_bfloat16 *)p, d1, d2, d3, d4);
     MDT_CHECK_CUDA(cudaGetLastError());
     return MDT_OK;
 }

@@ -334,12 +334,14 @@ def test_umma_descriptor_selftest():
     d1 = torch.zeros(128, 128, device="cuda")
     d2 = torch.zeros(128, 64, device="cuda")
     d3 = torch.zeros(128, 64, device="cuda")
-    _lib.check(lib.mdt_umma_selftest(*[_lib.ptr(t) for t in (a, b, p, v, at, bk, d1, d2, d3)], _lib.stream()),
+    d4 = torch.zeros(128, 64, device="cuda")
+    _lib.check(lib.mdt_umma_selftest(*[_lib.ptr(t) for t in (a, b, p, v, at, bk, d1, d2, d3, d4)], _lib.stream()),
                "mdt_umma_selftest")
     torch.cuda.synchronize()
     r1 = a.float() @ b.float().T
     r2 = p.float() @ v.float()
     r3 = at.float().T @ bk.float().T
-    for name, d, r in (("K-major x K-major", d1, r1), ("K-major x MN-major", d2, r2), ("MN-major x K-major", d3, r3)):
+    for name, d, r in (("K-major x K-major", d1, r1), ("K-major x MN-major", d2, r2), ("MN-major x K-major", d3, r3),
+                       ("A from tensor memory x MN-major", d4, r2)):
         err = float((d - r).abs().max())
         assert err < 1e-2, (name, err)
