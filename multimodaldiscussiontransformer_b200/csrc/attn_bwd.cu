@@ -543,10 +543,13 @@ extern "C" int mdt_biased_attn_bwd(const void *q, const void *k, const void *v, 
     const int B = d->B, H = d->H, T = d->T;
 
     const int mode = bias_mode(bias, bias_dtype, code);
-    const int Tmain = tail_split(T, mode == kBiasCode || mode == kBiasNone);
-    // code / no bias: warp-specialised kernel (attn_bwd2.cu); it computes delta itself unless the tail-key kernel needs the buffer
+    // code / no bias: warp-specialised kernel (attn_bwd2.cu); it computes delta itself.  MDT_ATTN_BWD=1 selects the older
+    // one-role kernel below (with its tail-key helper for T = 128 k + r) for A/B measurements.
     static const bool use_bwd2 = []() { const char *e = getenv("MDT_ATTN_BWD"); return !(e && e[0] == '1'); }();
     const bool bwd2 = use_bwd2 && (mode == kBiasNone || (mode == kBiasCode && code_t != nullptr));
+    // The tail-key split pays off for the one-role kernel only: with bwd2 the almost empty key tile of T = 128 k + r is a CTA
+    // whose dead warps skip the arithmetic (T = 129: 62 us without the split, 71 us with it and its two helper launches).
+    const int Tmain = tail_split(T, !bwd2 && (mode == kBiasCode || mode == kBiasNone));
     if (!bwd2 || Tmain < T) {  // delta = rowsum(dO * O)
         const int64_t rows = (int64_t)B * H * T;
         const int threads = 256, rows_per_block = threads / 8;

@@ -308,8 +308,6 @@ class _BiasedAttention(torch.autograd.Function):
                 _lib.ptr(transposed_code(code)) if code is not None else None, ctx.pitch, _lib.ptr(lut), _lib.ptr(key_pad), _lib.ptr(dq), _lib.ptr(dk), _lib.ptr(dv), ctypes.byref(gdims),
                 _lib.ptr(dq_accum), _lib.ptr(delta), _lib.ptr(g_bias), _lib.ptr(g_lut), ctx.drop[0], ctx.drop[1],
                 _lib.stream()), "mdt_biased_attn_bwd")
-        if bias is None and T > 128 and 1 <= T % 128 <= 8:  # + attn_bwd_tail_k_kernel (csrc/attn_tail.cu), for the launch count
-            _lib.CALLS["mdt_biased_attn_bwd:tail_keys"] = _lib.CALLS.get("mdt_biased_attn_bwd:tail_keys", 0) + 1
         return dq, dk, dv, g_bias, None, g_lut, None, None, None
 
 
