@@ -40,16 +40,26 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=8)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--batch", type=int, default=32, help="discussion graphs per GPU per step")
+    ap.add_argument("--batch", type=int, default=None, help="discussion graphs per GPU per micro-batch (default 32; 16 for cfg5)")
     ap.add_argument("--nodes", type=int, default=128, help="comments per graph")
     ap.add_argument("--image-frac", type=float, default=0.10)
     ap.add_argument("--pool", type=int, default=2, help="distinct pre-packed host batches cycled through")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="cfg3", choices=["cfg3", "cfg5"],
+                    help="cfg3 = BASELINE configs[2] (32 x 128 comments); cfg5 = configs[4] (trees of 16..512 comments, --batch 16)")
+    ap.add_argument("--update-freq", type=int, default=1, help="micro-batches per optimizer update (published run: 3)")
+    ap.add_argument("--grad-dtype", default="bf16", choices=["bf16", "fp32"], help="dtype of the all-reduced gradient buckets")
+    ap.add_argument("--no-overlap", action="store_true", help="one all-reduce after the backward instead of overlapped buckets")
+    ap.add_argument("--fp32-images", action="store_true", help="ship images as fp32 like the reference collator (default bf16)")
+    ap.add_argument("--fast", action="store_true", help="skip the T=1025 / preprocessing / CPU legs (development runs)")
     ap.add_argument("--prep", action="store_true",
                     help="configs[1] instead of the training step: Floyd-Warshall sweep (16-512 nodes, batch 256) and "
                          "GraphAttnBias GB/s, one JSON line per case, the CPU reference timed beside each APSP size")
     ap.add_argument("--prep-json", default=None)
-    return ap.parse_args()
+    a = ap.parse_args()
+    if a.batch is None:
+        a.batch = 32 if a.workload == "cfg3" else 16
+    return a
 
 
 def load_peaks():
@@ -201,7 +211,7 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    dropouts = (0.4, 0.0, 0.3)
+    dropouts = DROPOUTS   # same as the GPU arm
     cb, ms = cpu_reference_arm(args.nodes, args.steps, args.warmup, args.image_frac, dropouts)
     line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
@@ -213,19 +223,20 @@ def run_reference(args):
 
 def instep_traffic():
     """DRAM bytes (read + write) of the attention kernels of one forward + one backward call inside a cfg3 training step,
-    from the committed `ncu --set full` capture of bench.py (profiles/attn_instep_traffic_r01.json, tools/ncu_traffic.py);
-    None when the capture is absent."""
-    path = os.path.join(ROOT, "profiles", "attn_instep_traffic_r01.json")
-    if not os.path.isfile(path):
-        return None
-    try:
-        ks = json.load(open(path))["kernels"]
-        per_name = {}
-        for k in ks:  # one launch of each kernel kind
-            per_name.setdefault(k["name"], k["dram_bytes"])
-        return float(sum(per_name.values()))
-    except Exception:
-        return None
+    from the committed `ncu --set full` capture of bench.py (tools/ncu_traffic.py); None when the capture is absent."""
+    for name in ("attn_instep_traffic_r02.json", "attn_instep_traffic_r01.json"):
+        path = os.path.join(ROOT, "profiles", name)
+        if not os.path.isfile(path):
+            continue
+        try:
+            ks = json.load(open(path))["kernels"]
+            per_name = {}
+            for k in ks:  # one launch of each kernel kind
+                per_name.setdefault(k["name"], k["dram_bytes"])
+            return float(sum(per_name.values()))
+        except Exception:
+            continue
+    return None
 
 
 def attention_cfg4(peaks, T=1025, iters=10):
@@ -257,6 +268,63 @@ def attention_cfg4(peaks, T=1025, iters=10):
             "peak_kind": "burst bf16 (kernels timed alone)", "iters": iters}
 
 
+def prep_leg(peaks, iters=5):
+    """BASELINE.json configs[1] in the default line (<= ~5 s): the batched Floyd-Warshall kernel at 128 and 512 nodes
+    (batch 256, int64 M out) with a bit-exactness check of a sample against the reference's own Cython build
+    (oracle/_ref) or the C restatement, and GraphAttnBias forward / backward GB/s at N = 512."""
+    import numpy as np
+    import torch
+    sys.path.insert(0, os.path.join(ROOT, "benchmarks"))
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import prep_microbench as pm
+    from multimodaldiscussiontransformer_b200.data import algos
+
+    ref, kind = None, "port"
+    try:
+        import build_ref
+        ref = build_ref.load_ref_algos(build=False)
+        kind = "reference"
+    except Exception:
+        ref = None
+    import mdt_oracle as orc  # checker of the timed sample / CPU baseline
+
+    timer = pm.Timer()
+    mhz = 1965.0
+    try:
+        mhz = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("sm_max_mhz", mhz))
+    except Exception:
+        pass
+    alu_peak = pm.SM_COUNT * pm.LANES * 2 * mhz * 1e6
+    apsp = []
+    for n in (128, 512):
+        adj_np, depth = pm.tree_batch(n, 256)
+        adj = torch.from_numpy(adj_np).cuda()
+        M, _ = algos.floyd_warshall_batched(adj, False)
+        pm.check_apsp(M, depth)
+        ms = timer(lambda: algos.floyd_warshall_batched(adj, False), iters)
+        k = 4 if n == 128 else 1   # bounded CPU sample: n^3 work per graph
+        t0 = time.perf_counter()
+        outs = [(ref.floyd_warshall(adj_np[i].astype("int64")) if ref is not None else orc.floyd_warshall(adj_np[i].astype("int64")))
+                for i in range(k)]
+        cpu_ms = (time.perf_counter() - t0) / k * 1e3
+        exact = all(bool((M[i].cpu().numpy() == np.asarray(outs[i][0])).all()) for i in range(k))
+        relax = 256.0 * n ** 3
+        nbytes = 256.0 * n * n * 9
+        apsp.append({"n": n, "batch": 256, "us": ms * 1e3, "graphs_per_s": 256 / ms * 1e3, "relaxations_per_s": relax / ms * 1e3,
+                     "alu_frac": relax / (ms * 1e-3) / alu_peak, "hbm_gbs": nbytes / ms / 1e6,
+                     "bit_exact": exact, "checked_against": kind, "checked_graphs": k, "cpu_ms_per_graph": cpu_ms, "cpu_cores": 1})
+    rows = pm.attn_bias_sweep([(32, 512)], iters, timer)
+    bias = next(r for r in rows if r["dtype"] == "bfloat16")
+    return {
+        "apsp": {"bound": "integer ALU: 148 SMs x 128 lanes x 2 relaxations (VIADDMNMX.U16x2) x %.0f MHz = %.1f T relaxations/s" % (mhz, alu_peak / 1e12),
+                 "unit": "relaxations/s", "peak": alu_peak, "cases": apsp, "achieved": apsp[-1]["relaxations_per_s"],
+                 "frac": apsp[-1]["alu_frac"]},
+        "attn_bias": {"bound": "hbm", "unit": "GB/s", "peak": peaks["hbm_gbs"], "B": 32, "N": 512, "dtype": "bf16",
+                      "fwd_us": bias["fwd_us"], "bwd_us": bias["bwd_us"], "fwd_gbs": bias["fwd_gbs"], "bwd_gbs": bias["bwd_gbs"],
+                      "achieved": bias["fwd_gbs"], "frac": bias["fwd_frac"], "bwd_frac": bias["bwd_frac"]},
+    }
+
+
 # ---------------------------------------------------------------------------------------------
 # B200 arm
 # ---------------------------------------------------------------------------------------------
@@ -276,6 +344,26 @@ def build_model(device):
     model.encoder.graph_encoder.pack_text = os.environ.get("MDT_PACK_TEXT", "1") != "0"   # SURVEY 8f N1 (see config.text)
     crit = GraphPredictionNodeCrossEntropy(None, args.positive_weight, args.negative_weight).to(device)
     return args, model, crit
+
+
+def workload_sizes(args, rank, world):
+    """Comments per graph of this rank's batches (one list per pool entry) and the workload's name."""
+    import numpy as np
+
+    from multimodaldiscussiontransformer_b200.train import balanced_shards
+
+    B = args.batch
+    if args.workload == "cfg3":
+        return [[args.nodes] * B for _ in range(args.pool)], WORKLOAD
+    # BASELINE.json configs[4]: trees of up to 512 comments.  Every rank draws the same global list (B x world graphs per
+    # pool entry), the shards are balanced by comment count (sum T^2 / sum T), this rank takes its own.
+    out = []
+    for i in range(args.pool):
+        rng = np.random.default_rng(4242 + i)
+        sizes = rng.integers(16, 513, size=B * world).tolist()
+        out.append([sizes[j] for j in balanced_shards(sizes, world)[rank]])
+    return out, ("configs[4]: synthetic trees of 16..512 comments (uniform), %d graphs per GPU per step, padded to the largest "
+                 "tree of the batch, shards balanced by comment count, bf16" % B)
 
 
 def run_b200(args):
@@ -301,23 +389,36 @@ def run_b200(args):
 
     margs, model, crit = build_model(device)
     sched = PolynomialDecayLR(margs.lr, margs.end_learning_rate, margs.warmup_updates, margs.total_num_update)
+    grad_dtype = torch.bfloat16 if args.grad_dtype == "bf16" else torch.float32
     trainer = Trainer(model, crit, lr=margs.lr, betas=margs.adam_betas, eps=margs.adam_eps, weight_decay=margs.weight_decay,
-                      update_freq=1, lr_schedule=sched)
+                      update_freq=args.update_freq, lr_schedule=sched, grad_dtype=grad_dtype, overlap=not args.no_overlap)
     spmax = margs.spatial_pos_max
-    B, n = args.batch, args.nodes
+    B = args.batch
+    uf = args.update_freq
     # graphs are sharded by rank: every rank packs its own pool of batches (weak scaling)
-    pool = [HostBatch(syn.synthetic_items([n] * B, 7919 * (rank + 1) + i, image_frac=args.image_frac)) for i in range(args.pool)]
+    sizes_pool, workload = workload_sizes(args, rank, world)
+    img_dtype = torch.float32 if args.fp32_images else torch.bfloat16
+    pool = [HostBatch(syn.synthetic_items(sz, 7919 * (rank + 1) + i, image_frac=args.image_frac), image_dtype=img_dtype)
+            for i, sz in enumerate(sizes_pool)]
     resident = [RawBatch(hb, device) for hb in pool]
-    h2d = max(hb.nbytes() for hb in pool)
+    h2d = max(hb.nbytes() for hb in pool) * uf
+    copy_stream = torch.cuda.Stream(device=device)
 
     def step_resident(i):
-        bd = collate_device(resident[i % len(resident)], spmax)
-        return trainer.train_step([{"net_input": {"batched_data": bd}}])
+        mbs = [{"net_input": {"batched_data": collate_device(resident[(i * uf + k) % len(resident)], spmax)}} for k in range(uf)]
+        return trainer.train_step(mbs)
+
+    inflight = {}
+
+    def fetch(i):  # host -> HBM copies of step i's micro-batches on the copy stream
+        return [RawBatch(pool[(i * uf + k) % len(pool)], device, stream=copy_stream) for k in range(uf)]
 
     def step_e2e(i):
-        bd = collate_device(RawBatch(pool[i % len(pool)], device), spmax)   # pinned host -> HBM every step
-        stats = trainer.train_step([{"net_input": {"batched_data": bd}}])
-        return stats.cpu()                                                   # loss + counters back to the host
+        raws = inflight.pop(i, None) or fetch(i)
+        inflight[i + 1] = fetch(i + 1)          # the next step's batch crosses PCIe under this step's kernels
+        mbs = [{"net_input": {"batched_data": collate_device(r.wait(), spmax)}} for r in raws]
+        stats = trainer.train_step(mbs)
+        return stats.cpu()                      # loss + counters back to the host
 
     def barrier():
         if world > 1:
@@ -328,20 +429,24 @@ def run_b200(args):
         barrier()
         if record:
             ops.ATTN_EVENTS = []
+        comm = []
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0 = time.perf_counter()
         e0.record()
         for i in range(steps):
             fn(i)
+            if record and "comm_end" in trainer.timing:
+                comm.append((trainer.timing["backward_end"], trainer.timing["comm_end"]))
         e1.record()
         barrier()
         wall = (time.perf_counter() - t0) * 1e3
         ms = max(e0.elapsed_time(e1), 0.0)
         ev, ops.ATTN_EVENTS = ops.ATTN_EVENTS, None
-        t = torch.tensor([ms, wall], dtype=torch.float64, device=device)
+        exposed = sum(a_.elapsed_time(b_) for a_, b_ in comm) / max(len(comm), 1)
+        t = torch.tensor([ms, wall, exposed], dtype=torch.float64, device=device)
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t[0]), float(t[1]), ev
+        return float(t[0]), float(t[1]), ev, float(t[2])
 
     for i in range(args.warmup):
         step_resident(i)
@@ -349,39 +454,82 @@ def run_b200(args):
     if sampler:
         sampler.start()
     calls0 = _lib.kernel_launches()
-    ms_total, _, events = timed(step_resident, args.steps, record=True)
+    ms_total, _, events, exposed_comm_ms = timed(step_resident, args.steps, record=True)
     launches = _lib.kernel_launches() - calls0
     clocks = sampler.stop() if sampler else None
     for i in range(2):
         step_e2e(i)
-    _, e2e_wall, _ = timed(step_e2e, args.steps)
+    inflight.clear()
+    _, e2e_wall, _, _ = timed(step_e2e, args.steps)
+    inflight.clear()
     peak_mem = torch.cuda.max_memory_allocated() / 2 ** 30
 
-    graphs = B * world * args.steps
+    graphs = B * uf * world * args.steps
     value = graphs / (ms_total / 1e3)
     e2e_value = graphs / (e2e_wall / 1e3)
 
-    # ---- roofline of the dominant kernel of this library: biased attention (tensor pipe)
+    # ---- communication / copy costs measured alone (they explain the scaling numbers; not part of `value`)
+    allreduce_ms = None
+    if world > 1:
+        barrier()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record()
+        for _ in range(3):
+            dist.all_reduce(trainer.flat_grad)
+        a1.record()
+        barrier()
+        allreduce_ms = a0.elapsed_time(a1) / 3
+        trainer.flat_grad.zero_()
+    c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    c0.record()
+    RawBatch(pool[0], device)
+    c1.record()
+    torch.cuda.synchronize()
+    h2d_ms = c0.elapsed_time(c1) * uf
+
+    # ---- roofline of the north-star kernel of this library: biased graph attention (tensor pipe), in-step
     peaks = load_peaks()
-    fwd = [s.elapsed_time(e) for k, s, e, *_ in events if k == "fwd"]
-    bwd = [s.elapsed_time(e) for k, s, e, *_ in events if k == "bwd"]
-    T = n + 1
+    n_graph = max(sizes_pool[0])
+    T = n_graph + 1
+    fwd = [s.elapsed_time(e) for k, s, e, b_, h_, t_ in events if k == "fwd" and (b_, t_) == (B, T)]
+    bwd = [s.elapsed_time(e) for k, s, e, b_, h_, t_ in events if k == "bwd" and (b_, t_) == (B, T)]
     flop_fwd = 4.0 * B * 12 * T * T * 64          # 4*B*H*T^2*d, true T, S-recompute not counted
     flop_bwd = 8.0 * B * 12 * T * T * 64
-    fwd_ms, bwd_ms = statistics.mean(fwd), statistics.mean(bwd)
-    achieved = (flop_fwd + flop_bwd) / ((fwd_ms + bwd_ms) * 1e-3) / 1e12
-    roofline = {"bound": "tensor", "kernel": "attn_fwd_kernel + attn_bwd_kernel (biased attention, code+lut bias)",
-                "achieved": achieved, "peak": peaks["tf_sustained"], "unit": "TFLOP/s", "frac": achieved / peaks["tf_sustained"],
-                "traffic": instep_traffic(), "peak_source": peaks["source"] + ", sustained bf16", "fwd_us": fwd_ms * 1e3, "bwd_us": bwd_ms * 1e3,
-                "fwd_tflops": flop_fwd / (fwd_ms * 1e-3) / 1e12, "bwd_tflops": flop_bwd / (bwd_ms * 1e-3) / 1e12,
-                "launches_timed": len(fwd) + len(bwd), "attn_share_of_step": (sum(fwd) + sum(bwd)) / ms_total}
+    roofline = {"bound": "tensor", "kernel": "attn_fwd3_kernel + attn_bwd2_kernel (biased graph attention, code+lut bias, B=%d T=%d)" % (B, T),
+                "peak": peaks["tf_sustained"], "unit": "TFLOP/s", "peak_source": peaks["source"] + ", sustained bf16",
+                "traffic": instep_traffic() if args.workload == "cfg3" else None}
+    all_attn = sum(s.elapsed_time(e) for k, s, e, *_ in events if k in ("fwd", "bwd"))
+    if fwd and bwd:
+        fwd_ms, bwd_ms = statistics.mean(fwd), statistics.mean(bwd)
+        achieved = (flop_fwd + flop_bwd) / ((fwd_ms + bwd_ms) * 1e-3) / 1e12
+        roofline.update({"achieved": achieved, "frac": achieved / peaks["tf_sustained"], "fwd_us": fwd_ms * 1e3, "bwd_us": bwd_ms * 1e3,
+                         "fwd_tflops": flop_fwd / (fwd_ms * 1e-3) / 1e12, "bwd_tflops": flop_bwd / (bwd_ms * 1e-3) / 1e12,
+                         "launches_timed": len(fwd) + len(bwd), "attn_share_of_step": (sum(fwd) + sum(bwd)) / ms_total,
+                         "all_mdt_biased_attn_share_of_step": all_attn / ms_total})
 
-    # the LayerNorm kernels (HBM-bound) are the largest share of the step among this library's kernels
+    # packed text attention of the fusion layers (HBM-bound: q, k, v in + o out; q, k, v, o, dO in + dq, dk, dv out)
+    vl_f = [(s.elapsed_time(e), tot, h_) for k, s, e, tot, h_, nseq in events if k == "vl_fwd"]
+    vl_b = [(s.elapsed_time(e), tot, h_) for k, s, e, tot, h_, nseq in events if k == "vl_bwd"]
+    if vl_f and vl_b:
+        bf = sum(4.0 * tot * h_ * 64 * 2 for _, tot, h_ in vl_f)
+        bb = sum(8.0 * tot * h_ * 64 * 2 for _, tot, h_ in vl_b)
+        tf_, tb_ = sum(x[0] for x in vl_f), sum(x[0] for x in vl_b)
+        roofline["text_attention"] = {"bound": "hbm", "kernel": "attn_varlen_fwd_kernel + attn_varlen_bwd_kernel (packed text sequences)",
+                                      "achieved": (bf + bb) / ((tf_ + tb_) * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                                      "frac": (bf + bb) / ((tf_ + tb_) * 1e-3) / 1e9 / peaks["hbm_gbs"],
+                                      "fwd_us": tf_ / len(vl_f) * 1e3, "bwd_us": tb_ / len(vl_b) * 1e3,
+                                      "share_of_step": (tf_ + tb_) / ms_total}
+
+    # the LayerNorm kernels (HBM-bound)
     ln_b = ln_ms = 0.0
-    for k, s_, e_, rows_, C_, flags in events:
+    for ev in events:
+        k = ev[0]
         if k == "ln_fwd":
+            _, s_, e_, rows_, C_, flags = ev
             ln_b += rows_ * C_ * 2.0 * (2 + (flags >> 1) + (flags & 1)) + rows_ * 8.0   # x, y (+ residual) (+ z) + mean / rstd
         elif k == "ln_bwd":
+            _, s_, e_, rows_, C_, flags = ev
             ln_b += rows_ * C_ * 2.0 * (2 + flags) + rows_ * 8.0                         # dy, z, gradients written
         else:
             continue
@@ -395,26 +543,36 @@ def run_b200(args):
         if world > 1:
             dist.destroy_process_group()
         return
-    if world == 1:
+    if world == 1 and not args.fast:
         roofline["attn_T1025"] = attention_cfg4(peaks)
+        try:
+            roofline.update(prep_leg(peaks))
+        except Exception as ex:  # the prep leg must never cost the headline line
+            roofline["prep_error"] = "%s: %s" % (type(ex).__name__, str(ex)[:200])
     cpu = None
-    if not args.no_cpu_baseline and world == 1:
-        cpu, _ = cpu_reference_arm(n, 2, 1, args.image_frac, DROPOUTS)
+    if not args.no_cpu_baseline and world == 1 and not args.fast:
+        cpu, _ = cpu_reference_arm(args.nodes, 3, 1, args.image_frac, DROPOUTS)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "bf16", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "graphs_per_gpu": B, "comments_per_graph": n, "image_frac": args.image_frac,
+        "config": {"workload": workload, "graphs_per_gpu": B, "update_freq": uf,
+                   "comments_per_graph": args.nodes if args.workload == "cfg3" else "16..512 (padded to %d)" % n_graph,
+                   "image_frac": args.image_frac,
                    "model": "published run_train.sh 8 4 5 2 2: 8 fusion layers (stacks of 2), 10 executed graph layers, nb=4, "
-                            "spatial_pos_max=5, freeze_initial_encoders, AdamW fp32 master weights, update_freq 1",
+                            "spatial_pos_max=5, freeze_initial_encoders, AdamW fp32 master weights",
                    "dropout": {"dropout": DROPOUTS[0], "attention_dropout": DROPOUTS[1], "act_dropout": DROPOUTS[2]},
-                   "text": "fusion-layer BERT blocks on packed (unpadded) tokens: padding tokens (46 % of the batch) are not computed; "
-                           "logits / loss / gradients equal the padded path (tests/test_gpu_modules.py), MDT_PACK_TEXT=0 restores it",
-                   "note": "graph-layer attention dropout 0.3 runs inside the attention kernels (counter-hash mask, regenerated in the backward)",
+                   "text": "fusion-layer BERT blocks on packed (unpadded) tokens, attention on this library's packed-sequence kernels "
+                           "(MDT_TEXT_ATTN=flash / MDT_PACK_TEXT=0 restore the library call / the padded path for A/B runs)",
+                   "images": "shipped %s over PCIe (the model computes in bf16)" % ("fp32" if args.fp32_images else "bf16"),
+                   "comm": "gradient buckets (%s) all-reduced on a side stream while the backward runs" % args.grad_dtype
+                           if not args.no_overlap else "one all-reduce after the backward",
                    "l2": "working set per step (activations, weights) >> 126 MB L2; batches cycle through a pool",
                    "parallelism": f"dp{world}", "peak_mem_gib": round(peak_mem, 1)},
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": Trainer.N_STATS * 4},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": Trainer.N_STATS * 4,
+                "note": "step i+1's batch is copied from pinned memory on a copy stream while step i computes"},
         "gpu_launches": launches, "roofline": roofline, "clocks": clocks,
+        "h2d_ms": h2d_ms, "allreduce_ms": allreduce_ms, "exposed_comm_ms": exposed_comm_ms if world > 1 else 0.0,
     }
     if cpu is not None:
         line["cpu_baseline"] = cpu

@@ -7,9 +7,10 @@
   (SURVEY §8d ``tree(n, seed)``, seeds 0..batch-1), uint8 adjacency resident in HBM, int64 ``M`` out (the
   Cython signature's dtype), with and without the predecessor matrix.  Algorithmic work per graph: ``n^3``
   min-plus relaxations; algorithmic bytes ``n^2`` (adjacency) + ``8 n^2`` (``M``) [+ ``8 n^2`` for ``path``].
-  ``alu_frac`` is against ``148 SMs x 128 lanes x sm clock`` relaxations/s (one packed-uint16x2 add and one
-  ``vminu2`` per two relaxations = one relaxation per lane per clock); ``hbm_frac`` against the measured copy
-  bandwidth.  Size-independent checks after every launch: ``M`` symmetric, zero diagonal, ``M[0, i]`` = tree
+  ``alu_frac`` is against ONE stated integer-ALU bound, ``148 SMs x 128 lanes x 2 relaxations x max SM clock``
+  = 74 T relaxations/s: one ``VIADDMNMX.U16x2`` (packed add + min of two uint16 pairs = 2 relaxations) per lane per
+  clock, nothing else issued (the same denominator as DESIGN.md section 4; round 1 quoted 37 T/s here and 74 T/s
+  there); ``hbm_frac`` against the measured copy bandwidth.  Size-independent checks after every launch: ``M`` symmetric, zero diagonal, ``M[0, i]`` = tree
   depth, no entry above 510.  (Bit-exactness against the oracle is ``tests/test_gpu_graph_kernels.py``.)
 * GraphAttnBias (``mdt_attn_bias_fwd/bwd``, csrc/attn_bias.cu; graphormer_layers.py:86-110): algorithmic bytes
   forward ``B N^2 4 + B T^2 e`` read + ``B H T^2 e`` written, backward ``B H T^2 e + B N^2 4`` read.
@@ -79,7 +80,7 @@ def check_apsp(M: torch.Tensor, depth: np.ndarray):
 
 def apsp_sweep(sizes, batch, iters, timer, cpu_fn=None):
     hbm, mhz, src = peaks()
-    alu_peak = SM_COUNT * LANES * mhz * 1e6  # relaxations / s
+    alu_peak = SM_COUNT * LANES * 2 * mhz * 1e6  # relaxations / s: one VIADDMNMX.U16x2 (2 relaxations) per lane-clock
     rows = []
     for n in sizes:
         adj_np, depth = tree_batch(n, batch)

@@ -148,7 +148,10 @@ class HostBatch:
     """One batch packed into pinned host buffers by the dataloader side (no CUDA calls; safe in forked workers
     when ``pin=False``).  ``tensors`` is what crosses PCIe each step."""
 
-    def __init__(self, items: List[Any], pin: bool = True):
+    def __init__(self, items: List[Any], pin: bool = True, image_dtype: torch.dtype = torch.float32):
+        """``image_dtype``: dtype the images cross PCIe in.  The reference ships fp32 (collator.py:144-148); the model casts
+        them to its compute dtype before the first ViT layer anyway (multigraphormer_graph_encoder.py: ``x_images.to(dtype)``),
+        so a bf16 model loses nothing by staging them as bf16 -- and 97 % of a batch's bytes are images."""
         items = [it for it in items if it is not None]                      # dataset.py:160,195
         self.B = len(items)
         self.sizes = [int(_np(it.x["input_ids"]).shape[0]) for it in items]
@@ -192,7 +195,7 @@ class HostBatch:
             o += n
         imgs = [it.x_images if isinstance(it.x_images, torch.Tensor) else torch.from_numpy(_np(it.x_images)) for it in items]
         imgs = [im for im in imgs if not bool(torch.all(im.eq(0)))]          # collator.py:144
-        images = torch.cat(imgs) if imgs else None
+        images = torch.cat(imgs).to(image_dtype) if imgs else None
         flags = torch.from_numpy(np.stack([has_img, np.concatenate(
             [_np(getattr(it, "y_mask", None) if getattr(it, "y_mask", None) is not None else np.zeros(n, bool)).reshape(-1)
              for it, n in zip(items, ns)]).astype(bool)]))                    # [2, n_real] bool: image flag, y_mask
@@ -207,12 +210,33 @@ class HostBatch:
 
 
 class RawBatch:
-    """The same buffers resident in HBM (``HostBatch.tensors`` after one async copy each)."""
+    """The same buffers resident in HBM (``HostBatch.tensors`` after one async copy each).
 
-    def __init__(self, host: HostBatch, device):
+    With ``stream`` the copies are issued on that (copy) stream, so the batch of step i+1 crosses PCIe under the
+    kernels of step i; ``wait()`` makes the consumer's current stream wait for them and tells the caching allocator
+    that the buffers are in use there."""
+
+    def __init__(self, host: HostBatch, device, stream=None):
         self.host = host
         self.device = device
-        self.t = {k: (v.to(device, non_blocking=True) if v is not None else None) for k, v in host.tensors.items()}
+        self.ready = None
+        if stream is None:
+            self.t = {k: (v.to(device, non_blocking=True) if v is not None else None) for k, v in host.tensors.items()}
+        else:
+            with torch.cuda.stream(stream):
+                self.t = {k: (v.to(device, non_blocking=True) if v is not None else None) for k, v in host.tensors.items()}
+                self.ready = torch.cuda.Event()
+                self.ready.record(stream)
+
+    def wait(self) -> "RawBatch":
+        if self.ready is not None:
+            cur = torch.cuda.current_stream(self.device)
+            cur.wait_event(self.ready)
+            for v in self.t.values():
+                if v is not None:
+                    v.record_stream(cur)
+            self.ready = None
+        return self
 
 
 def collate_device(raw: RawBatch, spatial_pos_max: int = 10) -> Dict[str, Any]:
