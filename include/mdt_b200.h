@@ -245,6 +245,17 @@ int mdt_dropout_add_ln_bwd(const void *dy, const void *z, const float *mean, con
                            void *dx, void *dres, float *dgamma, float *dbeta, int64_t rows, int C, float p,
                            uint64_t seed, mdt_stream_t stream);
 
+/* ------------------------------------------------------------------------------------
+ * N2  GELU of the feed-forward blocks (exact erf form, fp32 arithmetic on bf16 tensors)
+ *     mDT/src/modules/graphormer_graph_encoder_layer.py:132-136 (fc1 -> gelu(x.float()).type_as(x)); Hugging Face
+ *     BertIntermediate / ViTIntermediate called from mDT/src/modules/multi_graphormer_fusion_layer.py:94-98,138-148
+ *   forward : g = u * Phi(u)                                   u, g bf16 [rows, C], C a multiple of 8
+ *   backward: du = dg * (Phi(u) + u phi(u));  dbias[c] += sum_r du[r,c]   (f32 [C], accumulated; NULL to skip) --
+ *             the bias gradient of the dense layer in front of the activation, without a further pass over du.
+ * ------------------------------------------------------------------------------------ */
+int mdt_gelu_fwd(const void *u, void *g, int64_t rows, int C, mdt_stream_t stream);
+int mdt_gelu_bwd(const void *dg, const void *u, void *du, float *dbias, int64_t rows, int C, mdt_stream_t stream);
+
 /* Self-test of the tcgen05 building blocks (shared-memory descriptor layouts, TMA 128-byte
  * swizzle, TMEM read-back); called by tests/ only.  All operands bf16, row major:
  *   d1[128,128] = a[128,64] * b[128,64]^T          (A and B K-major, both via TMA)

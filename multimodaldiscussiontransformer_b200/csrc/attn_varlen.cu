@@ -82,38 +82,47 @@ __device__ __forceinline__ VlUnit vl_unit(const VarlenArgs &a, int w) {
 // ------------------------------------------------------------------------------------------------ plan
 // Greedy grouping of consecutive sequences into <= 128-row items by thread 0 (the loop-carried state is a register and the
 // cu loads do not depend on it), then all threads fill the per-row windows.  Built once per batch.
+constexpr int kPlanSmemSeqs = 11 * 1024;  // cu_seqlens of up to 11263 sequences staged in shared memory (44 KB)
+
 __global__ void __launch_bounds__(1024) varlen_plan_kernel(const int32_t *__restrict__ cu, int n_seq, int group, int32_t *__restrict__ plan) {
+    __shared__ int32_t s_cu[kPlanSmemSeqs];
     int32_t *items = plan + plan_items_off();
     int32_t *seq_row0 = plan + plan_scratch_off(n_seq);
     int32_t *rowwin = plan + plan_rows_off(n_seq);
+    const bool staged = n_seq + 1 <= kPlanSmemSeqs;   // the serial pass then reads shared memory (29 cycles) instead of L2
+    if (staged)
+        for (int i = threadIdx.x; i <= n_seq; i += blockDim.x) s_cu[i] = cu[i];
+    __syncthreads();
+    const int32_t *c = staged ? s_cu : cu;
     if (threadIdx.x == 0) {
         int n_items = 0, err = 0;
-        int start_row = cu[0], s_first = 0;
+        int prev = c[0], start_row = prev, s_first = 0;
         for (int s = 0; s < n_seq; ++s) {
-            const int end = cu[s + 1];
-            if (end - cu[s] > 128) err = 1;  // a sequence longer than one tile: not this kernel's case
+            const int end = c[s + 1];
+            if (end - prev > 128) err = 1;  // a sequence longer than one tile: not this kernel's case
             if (s > s_first && (!group || end - start_row > 128)) {  // sequence s does not fit any more: close the item before it
                 items[2 * n_items] = start_row;
                 items[2 * n_items + 1] = s_first;
                 ++n_items;
                 s_first = s;
-                start_row = cu[s];
+                start_row = prev;
             }
             seq_row0[s] = start_row;
+            prev = end;
         }
         items[2 * n_items] = start_row;
         items[2 * n_items + 1] = s_first;
         ++n_items;
-        items[2 * n_items] = cu[n_seq];
+        items[2 * n_items] = prev;
         items[2 * n_items + 1] = n_seq;
         plan[0] = n_items;
         plan[1] = err;
         plan[2] = n_seq;
-        plan[3] = cu[n_seq];
+        plan[3] = prev;
     }
     __syncthreads();
     for (int s = threadIdx.x; s < n_seq; s += blockDim.x) {
-        const int a = cu[s], b = cu[s + 1], r0 = seq_row0[s];
+        const int a = c[s], b = c[s + 1], r0 = seq_row0[s];
         const int32_t win = (a - r0) | ((b - r0) << 16);
         for (int g = a; g < b; ++g) rowwin[g] = win;
     }

@@ -29,6 +29,7 @@ class GraphormerGraphEncoderLayer(nn.Module):
         self.pre_layernorm = pre_layernorm
         self.dropout_module = FairseqDropout(dropout, module_name=self.__class__.__name__)
         self.activation_dropout_module = FairseqDropout(activation_dropout, module_name=self.__class__.__name__)
+        self.activation_name = activation_fn
         self.activation_fn = get_activation_fn(activation_fn)
         self.self_attn = self.build_self_attention(self.embedding_dim, num_attention_heads, dropout=attention_dropout,
                                                    self_attention=True, q_noise=q_noise, qn_block_size=qn_block_size)
@@ -59,7 +60,13 @@ class GraphormerGraphEncoderLayer(nn.Module):
         residual = x
         if self.pre_layernorm:
             x = self.final_layer_norm(x)
-        x = self.activation_dropout_module(self.activation_fn(self.fc1(x)))
+        if (self.activation_name == "gelu" and x.is_cuda and x.dtype == torch.bfloat16 and self.fc1.weight.dtype == torch.bfloat16
+                and self.fc1.out_features % 8 == 0):
+            # fc1 -> gelu (fp32 arithmetic, as fairseq's) on csrc/gelu.cu: one pass instead of cast / gelu / cast, and the
+            # backward produces the activation gradient and fc1's bias gradient together
+            x = self.activation_dropout_module(ops.linear_gelu(x, self.fc1.weight, self.fc1.bias))
+        else:
+            x = self.activation_dropout_module(self.activation_fn(self.fc1(x)))
         x = self._add_norm(self.fc2(x), residual, self.final_layer_norm)
         return x, attn
 

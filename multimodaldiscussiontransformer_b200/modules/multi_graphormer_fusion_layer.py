@@ -121,15 +121,14 @@ def _varlen_attention(qkv, pack, dropout_p: float):
 def packed_bert_layer(layer, x: torch.Tensor, pack) -> torch.Tensor:
     """Hugging Face ``BertLayer`` arithmetic (post-LN block, same parameters, same dropout rates) on packed tokens.
 
-    The three projections run as ONE GEMM over the row-concatenated ``query / key / value`` weights (the parameters stay
-    separate, state-dict keys unchanged): ``x`` is read once, and the backward has one input-gradient GEMM and one
+    The three projections run as ONE GEMM over the fused storage of the ``query / key / value`` parameters
+    (``ops.linear_qkv``: the parameters keep their names and shapes, only their ``.data`` become adjacent slices of one
+    buffer): ``x`` is read once, no weights are concatenated per call, and the backward has one input-gradient GEMM and one
     bias-gradient reduction instead of three of each plus two gradient-accumulation adds over ``[total, C]``."""
     att, sa = layer.attention, layer.attention.self
     H = sa.num_attention_heads
     d = x.shape[-1] // H
-    w = torch.cat([sa.query.weight, sa.key.weight, sa.value.weight], 0)
-    b = torch.cat([sa.query.bias, sa.key.bias, sa.value.bias], 0)
-    qkv = torch.nn.functional.linear(x, w, b).view(-1, 3, H, d)
+    qkv = ops.linear_qkv(x, sa.query, sa.key, sa.value).view(-1, 3, H, d)
     ctx = _varlen_attention(qkv, pack, sa.dropout.p if layer.training else 0.0).reshape(x.shape)
     if x.dtype == torch.bfloat16 and x.shape[-1] in (256, 512, 768, 1024):
         # dense -> dropout -> + residual -> LayerNorm tails in one pass each way (libmdt_b200, csrc/layernorm.cu)
@@ -215,6 +214,32 @@ def use_mdt_attention(module: nn.Module) -> nn.Module:
     return module
 
 
+class FusedIntermediate(nn.Module):
+    """Hugging Face ``BertIntermediate`` / ``ViTIntermediate`` (``dense`` -> exact GELU; same parameters and state-dict keys)
+    whose bf16 CUDA forward is ``ops.linear_gelu``: the activation is one pass of csrc/gelu.cu and its backward also
+    yields the bias gradient of ``dense``; anything else takes Hugging Face's own forward."""
+
+    def forward(self, hidden_states):
+        d = self.dense
+        if (hidden_states.is_cuda and hidden_states.dtype == torch.bfloat16 and d.weight.dtype == torch.bfloat16
+                and d.out_features % 8 == 0 and getattr(self, "_mdt_exact_gelu", False)):
+            return ops.linear_gelu(hidden_states, d.weight, d.bias)
+        return self.intermediate_act_fn(d(hidden_states))
+
+
+def use_fused_intermediates(module: nn.Module) -> nn.Module:
+    """Re-class the ``dense -> gelu`` blocks below ``module`` whose activation is the exact (erf) GELU."""
+    from transformers.activations import GELUActivation
+
+    for m in module.modules():
+        if type(m).__name__ in ("BertIntermediate", "ViTIntermediate") and hasattr(m, "dense"):
+            act = getattr(m, "intermediate_act_fn", None)
+            exact = (isinstance(act, GELUActivation) and not getattr(act, "use_gelu_python", False)) or act is torch.nn.functional.gelu
+            m._mdt_exact_gelu = bool(exact)
+            m.__class__ = type("Fused" + type(m).__name__, (FusedIntermediate, type(m)), {})
+    return module
+
+
 def use_fused_layer_norms(module: nn.Module) -> nn.Module:
     """Re-class every plain ``nn.LayerNorm`` below ``module`` (the ViT blocks are pre-LN: no residual to fuse)."""
     for m in module.modules():
@@ -226,8 +251,8 @@ def use_fused_layer_norms(module: nn.Module) -> nn.Module:
 class GraphFusionLayer(nn.Module):
     def __init__(self, bert_layer, vit_layer, num_bottle_neck_tokens: int, use_projection: bool = False) -> None:
         super().__init__()
-        self.bert_encoder = bert_layer
-        self.vit_encoder = use_mdt_attention(use_fused_layer_norms(vit_layer))
+        self.bert_encoder = use_fused_intermediates(bert_layer)
+        self.vit_encoder = use_fused_intermediates(use_mdt_attention(use_fused_layer_norms(vit_layer)))
         self.gradient_checkpointing = False
         self.num_bottle_neck_tokens = num_bottle_neck_tokens
         if use_projection:  # constructed, never applied (multi_graphormer_fusion_layer.py:22-27)

@@ -59,18 +59,21 @@ class MultiheadAttention(nn.Module):
 
     # ------------------------------------------------------------------------------------
     def _project_qkv(self, x: Tensor):
-        """One [3C, C] GEMM; the d^-0.5 scaling of q (multihead_attention.py:137) is folded into its rows."""
-        w = torch.cat([self.q_proj.weight * self.scaling, self.k_proj.weight, self.v_proj.weight], dim=0)
-        b = None
-        if self.q_proj.bias is not None:
-            b = torch.cat([self.q_proj.bias * self.scaling, self.k_proj.bias, self.v_proj.bias], dim=0)
+        """One [3C, C] GEMM over the fused parameter storage of q_proj / k_proj / v_proj (``ops.linear_qkv``: no ``cat`` of
+        the weights per forward, the weight gradient comes back as three slices); q is then scaled by d^-0.5
+        (multihead_attention.py:137)."""
         T, B, C = x.shape
-        qkv = F.linear(x, w, b).view(T, B, 3, self.num_heads, self.head_dim)
+        if x.is_cuda:
+            qkv = ops.linear_qkv(x, self.q_proj, self.k_proj, self.v_proj)
+        else:  # host-side checks of the module logic (no kernels involved)
+            qkv = torch.cat([self.q_proj(x), self.k_proj(x), self.v_proj(x)], dim=-1)
+        qkv = qkv.view(T, B, 3, self.num_heads, self.head_dim)
         if qkv.dtype != torch.bfloat16:
             qkv = qkv.to(torch.bfloat16)
         if self.head_dim != KERNEL_HEAD_DIM:  # zero-padded head dim: same scores, same outputs
             qkv = F.pad(qkv, (0, KERNEL_HEAD_DIM - self.head_dim))
-        return tuple(qkv[:, :, i].permute(1, 0, 2, 3) for i in range(3))  # [B, T, H, 64] views
+        q = (qkv[:, :, 0] * self.scaling).permute(1, 0, 2, 3)
+        return q, qkv[:, :, 1].permute(1, 0, 2, 3), qkv[:, :, 2].permute(1, 0, 2, 3)  # [B, T, H, 64] views
 
     def forward(self, query, key: Optional[Tensor], value: Optional[Tensor],
                 attn_bias: Union[Tensor, FusedAttnBias, None], key_padding_mask: Optional[Tensor] = None,

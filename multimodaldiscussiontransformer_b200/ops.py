@@ -495,3 +495,142 @@ def dropout_add_layer_norm(x, residual, weight, bias, p: float = 0.0, training: 
     p = float(p) if training else 0.0
     seed = next_seed() if p > 0.0 else 0
     return _DropoutAddLayerNorm.apply(x, residual, weight, bias, p, eps, seed)
+
+
+# ------------------------------------------------------------------------------------------
+# N2  GELU (exact erf) and dense -> GELU with the bias gradient folded into the activation's backward
+#     graphormer_graph_encoder_layer.py:132-136; HF BertIntermediate / ViTIntermediate
+# ------------------------------------------------------------------------------------------
+def _gelu_ok(x: torch.Tensor) -> bool:
+    return x.is_cuda and x.dtype == torch.bfloat16 and x.shape[-1] % 8 == 0
+
+
+class _Gelu(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, u):
+        lib = _lib.load()
+        u2 = u.reshape(-1, u.shape[-1]).contiguous()
+        g = torch.empty_like(u2)
+        with torch.cuda.device(u.device):
+            _lib.check(lib.mdt_gelu_fwd(_lib.ptr(u2), _lib.ptr(g), u2.shape[0], u2.shape[1], _lib.stream()), "mdt_gelu_fwd")
+        ctx.save_for_backward(u2)
+        return g.view(u.shape)
+
+    @staticmethod
+    def backward(ctx, dg):
+        (u2,) = ctx.saved_tensors
+        lib = _lib.load()
+        dg2 = dg.reshape(u2.shape).contiguous()
+        du = torch.empty_like(u2)
+        with torch.cuda.device(dg.device):
+            _lib.check(lib.mdt_gelu_bwd(_lib.ptr(dg2), _lib.ptr(u2), _lib.ptr(du), None, u2.shape[0], u2.shape[1], _lib.stream()),
+                       "mdt_gelu_bwd")
+        return du.view(dg.shape)
+
+
+def gelu(u: torch.Tensor) -> torch.Tensor:
+    """Exact (erf) GELU of a bf16 CUDA tensor, arithmetic in fp32 (``F.gelu(u.float()).type_as(u)``)."""
+    if not _gelu_ok(u):
+        raise RuntimeError("ops.gelu: bf16 CUDA tensors with a last dimension that is a multiple of 8 (no other path)")
+    return _Gelu.apply(u)
+
+
+class _LinearGelu(torch.autograd.Function):
+    """``gelu(x @ W^T + b)``: the GEMMs stay cuBLAS (bias in its epilogue); the activation and, in the backward, the
+    activation gradient together with the bias gradient (column sums) are one pass each of csrc/gelu.cu."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias):
+        lib = _lib.load()
+        x2 = x.reshape(-1, x.shape[-1])
+        u = torch.nn.functional.linear(x2, weight, bias)
+        g = torch.empty_like(u)
+        with torch.cuda.device(x.device):
+            _lib.check(lib.mdt_gelu_fwd(_lib.ptr(u), _lib.ptr(g), u.shape[0], u.shape[1], _lib.stream()), "mdt_gelu_fwd")
+        ctx.save_for_backward(x2, weight, u)
+        ctx.has_bias = bias is not None
+        ctx.bias_dtype = bias.dtype if bias is not None else None
+        return g.view(*x.shape[:-1], weight.shape[0])
+
+    @staticmethod
+    def backward(ctx, dg):
+        x2, weight, u = ctx.saved_tensors
+        lib = _lib.load()
+        dg2 = dg.reshape(u.shape).contiguous()
+        du = torch.empty_like(u)
+        need_b = ctx.has_bias and ctx.needs_input_grad[2]
+        dbias = torch.zeros(u.shape[1], dtype=torch.float32, device=u.device) if need_b else None
+        with torch.cuda.device(dg.device):
+            _lib.check(lib.mdt_gelu_bwd(_lib.ptr(dg2), _lib.ptr(u), _lib.ptr(du), _lib.ptr(dbias), u.shape[0], u.shape[1],
+                                        _lib.stream()), "mdt_gelu_bwd")
+        dx = (du @ weight).view(*dg.shape[:-1], weight.shape[1]) if ctx.needs_input_grad[0] else None
+        dw = du.t() @ x2 if ctx.needs_input_grad[1] else None
+        return dx, dw, dbias.to(ctx.bias_dtype) if need_b else None
+
+
+def linear_gelu(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor]) -> torch.Tensor:
+    """``gelu(F.linear(x, weight, bias))`` for bf16 CUDA tensors (exact GELU in fp32)."""
+    if not (_gelu_ok(x) and weight.dtype == torch.bfloat16 and weight.shape[0] % 8 == 0):
+        raise RuntimeError("ops.linear_gelu: bf16 CUDA tensors, output width a multiple of 8 (no other path)")
+    return _LinearGelu.apply(x, weight, bias)
+
+
+# ------------------------------------------------------------------------------------------
+# N2  q / k / v projections as ONE GEMM over a persistent fused parameter view
+#     multihead_attention.py:134-136; HF BertSelfAttention.query / key / value
+# ------------------------------------------------------------------------------------------
+def fused_qkv_storage(q_lin, k_lin, v_lin):
+    """Make the weights (and biases) of three ``nn.Linear`` adjacent slices of one buffer and return the fused views
+    ``([3C, C], [3C] | None)``.  The parameters keep their names, shapes and identity (state-dict keys unchanged: only
+    ``.data`` is re-pointed, once); the fused views feed a single GEMM without a ``torch.cat`` per forward, and the weight
+    gradient of that GEMM is handed back as three slices without a copy.  Re-checked on every call (three pointer
+    compares): ``module.to(...)`` re-allocates parameters, after which the storage is fused again."""
+    ws = (q_lin.weight, k_lin.weight, v_lin.weight)
+    n, esz = ws[0].numel(), ws[0].element_size()
+    base = ws[0].data_ptr()
+    cache = getattr(q_lin, "_mdt_fused", None)
+    ok = (cache is not None and cache[0].data_ptr() == base and ws[1].data_ptr() == base + n * esz
+          and ws[2].data_ptr() == base + 2 * n * esz and cache[0].dtype == ws[0].dtype)
+    if not ok:
+        with torch.no_grad():
+            wf = torch.cat([w.data for w in ws], dim=0)
+            C = ws[0].shape[0]
+            for i, w in enumerate(ws):
+                w.data = wf[i * C:(i + 1) * C]
+            bf = None
+            if q_lin.bias is not None:
+                bs = (q_lin.bias, k_lin.bias, v_lin.bias)
+                bf = torch.cat([b.data for b in bs], dim=0)
+                for i, b in enumerate(bs):
+                    b.data = bf[i * C:(i + 1) * C]
+        cache = (wf, bf)
+        q_lin._mdt_fused = cache
+    return cache
+
+
+class _Linear3(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, wq, wk, wv, bq, bk, bv, wf, bf):
+        x2 = x.reshape(-1, x.shape[-1])
+        y = torch.nn.functional.linear(x2, wf, bf)
+        ctx.save_for_backward(x2, wf)
+        ctx.has_bias = bf is not None
+        return y.view(*x.shape[:-1], wf.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, wf = ctx.saved_tensors
+        dy2 = dy.reshape(-1, wf.shape[0])
+        C = wf.shape[0] // 3
+        dx = (dy2 @ wf).view(*dy.shape[:-1], wf.shape[1]) if ctx.needs_input_grad[0] else None
+        dw = dy2.t() @ x2 if any(ctx.needs_input_grad[1:4]) else None
+        db = dy2.sum(0) if ctx.has_bias and any(ctx.needs_input_grad[4:7]) else None
+        gw = [dw[i * C:(i + 1) * C] if dw is not None else None for i in range(3)]
+        gb = [db[i * C:(i + 1) * C] if db is not None else None for i in range(3)]
+        return (dx, *gw, *gb, None, None)
+
+
+def linear_qkv(x: torch.Tensor, q_lin, k_lin, v_lin) -> torch.Tensor:
+    """``cat([q_lin(x), k_lin(x), v_lin(x)], -1)`` as one GEMM over the fused parameter storage (no per-call ``cat``)."""
+    wf, bf = fused_qkv_storage(q_lin, k_lin, v_lin)
+    return _Linear3.apply(x, q_lin.weight, k_lin.weight, v_lin.weight, q_lin.bias, k_lin.bias, v_lin.bias, wf, bf)

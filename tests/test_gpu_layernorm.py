@@ -87,3 +87,63 @@ def test_layer_norm_rejects_other_dtypes_and_widths():
     wb = torch.ones(640, device="cuda").bfloat16()
     with pytest.raises(RuntimeError):
         ops.dropout_add_layer_norm(xb, None, wb, wb)
+
+
+# ---------------------------------------------------------------------------------------------
+# N2: GELU kernels (csrc/gelu.cu) and dense -> GELU with the bias gradient folded into the activation's backward
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("rows,C", [(1, 8), (37, 768), (1000, 3072), (4099, 96)])
+def test_gelu_forward_backward_vs_torch(rows, C):
+    """Exact-erf GELU in fp32 on bf16 tensors: equal to ``F.gelu(u.float()).bfloat16()`` up to one bf16 ulp of the result;
+    gradient against fp32 autograd <= 1e-2 relative Frobenius."""
+    from multimodaldiscussiontransformer_b200 import ops
+
+    g = torch.Generator(device="cuda").manual_seed(rows + C)
+    u = (torch.randn(rows, C, device="cuda", generator=g) * 2.5).bfloat16().requires_grad_(True)
+    y = ops.gelu(u)
+    ref = torch.nn.functional.gelu(u.detach().float())
+    assert float((y.float() - ref).abs().max()) <= 2e-2 and rel(y, ref) <= 4e-3
+    go = torch.randn(rows, C, device="cuda", generator=g).bfloat16()
+    (gu,) = torch.autograd.grad(y, u, go)
+    ur = u.detach().float().requires_grad_(True)
+    (gr,) = torch.autograd.grad(torch.nn.functional.gelu(ur), ur, go.float())
+    assert rel(gu, gr) <= 1e-2
+    # extreme arguments: no NaN, the right limits
+    x = torch.tensor([[-50.0, -8.0, -0.0, 0.0, 8.0, 50.0, 1e-4, -1e-4]], device="cuda").bfloat16()
+    out = ops.gelu(x).float()
+    assert bool(torch.isfinite(out).all()) and float(out[0, 0]) == 0.0 and float(out[0, 5]) == 50.0 and float(out[0, 2]) == 0.0
+
+
+def test_linear_gelu_and_linear_qkv_match_autograd():
+    from multimodaldiscussiontransformer_b200 import ops
+
+    g = torch.Generator(device="cuda").manual_seed(3)
+    rows, C, F_ = 777, 256, 1024
+    x = torch.randn(rows, C, device="cuda", generator=g).bfloat16().requires_grad_(True)
+    lin = torch.nn.Linear(C, F_).cuda().bfloat16()
+    y = ops.linear_gelu(x, lin.weight, lin.bias)
+    go = torch.randn(rows, F_, device="cuda", generator=g).bfloat16()
+    gx, gw, gb = torch.autograd.grad(y, [x, lin.weight, lin.bias], go)
+    xr = x.detach().float().requires_grad_(True)
+    wr, br = lin.weight.detach().float().requires_grad_(True), lin.bias.detach().float().requires_grad_(True)
+    yr = torch.nn.functional.gelu(torch.nn.functional.linear(xr, wr, br))
+    rx, rw, rb = torch.autograd.grad(yr, [xr, wr, br], go.float())
+    assert rel(y, yr) <= 6e-3
+    for a, b in ((gx, rx), (gw, rw), (gb, rb)):
+        assert rel(a, b) <= 1.5e-2
+    # three projections over the fused parameter storage
+    q, k, v = (torch.nn.Linear(C, C).cuda().bfloat16() for _ in range(3))
+    keys_before = [p.data_ptr() for p in (q.weight, k.weight, v.weight)]
+    want = torch.cat([q(x), k(x), v(x)], dim=-1)
+    got = ops.linear_qkv(x, q, k, v)
+    assert k.weight.data_ptr() == q.weight.data_ptr() + q.weight.numel() * 2          # adjacent now
+    assert torch.equal(got, want)
+    go3 = torch.randn_like(got)
+    grads = torch.autograd.grad(got, [x, q.weight, k.weight, v.weight, q.bias, k.bias, v.bias], go3)
+    ref = torch.autograd.grad(torch.cat([q(x), k(x), v(x)], dim=-1), [x, q.weight, k.weight, v.weight, q.bias, k.bias, v.bias], go3)
+    for a, b in zip(grads, ref):
+        assert rel(a, b) <= 1e-2
+    q.float(), k.float(), v.float()                                                    # re-allocation breaks adjacency ...
+    q.bfloat16(), k.bfloat16(), v.bfloat16()
+    assert torch.equal(ops.linear_qkv(x, q, k, v), torch.cat([q(x), k(x), v(x)], dim=-1))   # ... and the view is rebuilt
+    assert keys_before is not None
