@@ -88,6 +88,7 @@ def main():
     ap.add_argument("--fusion-shapes", action="store_true", help="also (B'=4096,T=104) text and (410,201) image shapes")
     ap.add_argument("--no-flush", action="store_true")
     ap.add_argument("--json", default=None)
+    ap.add_argument("--dropout", type=float, default=0.0, help="attention dropout probability (mask regenerated in the backward)")
     ap.add_argument("--no-lut-grad", action="store_true", help="code mode without the LUT gradient (no binning)")
     a = ap.parse_args()
     burst, sustained, src = peaks()
@@ -100,6 +101,8 @@ def main():
         q, k, v, kw = make_inputs(B, H, T, a.mode)
         if a.no_lut_grad and "lut" in kw:
             kw["lut"] = kw["lut"].detach()
+        if a.dropout > 0:
+            kw.update(dropout_p=a.dropout, seed=1234567)
         o = ops.biased_attention(q, k, v, **kw)
         go = torch.randn_like(o)
         inputs = [q, k, v] + [t for t in (kw.get("lut"), kw.get("bias")) if t is not None and t.requires_grad]
@@ -114,7 +117,7 @@ def main():
         f_ms = time_it(fwd, a.iters, flush, "fwd")
         b_ms = time_it(bwd, a.iters, flush, "bwd")
         ff, fb = 4.0 * B * H * T * T * 64, 8.0 * B * H * T * T * 64
-        row = dict(B=B, H=H, T=T, mode=a.mode, fwd_us=f_ms * 1e3, bwd_us=b_ms * 1e3, fwd_tflops=ff / f_ms / 1e9,
+        row = dict(B=B, H=H, T=T, mode=a.mode, dropout=a.dropout, fwd_us=f_ms * 1e3, bwd_us=b_ms * 1e3, fwd_tflops=ff / f_ms / 1e9,
                    bwd_tflops=fb / b_ms / 1e9, fwd_frac_burst=ff / f_ms / 1e9 / burst, bwd_frac_burst=fb / b_ms / 1e9 / burst,
                    fwd_bwd_tflops=(ff + fb) / (f_ms + b_ms) / 1e9, peak_burst=burst, peak_sustained=sustained, peak_source=src,
                    l2_flushed=flush is not None)

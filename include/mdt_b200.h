@@ -256,6 +256,13 @@ int mdt_dropout_add_ln_bwd(const void *dy, const void *z, const float *mean, con
 int mdt_gelu_fwd(const void *u, void *g, int64_t rows, int C, mdt_stream_t stream);
 int mdt_gelu_bwd(const void *dg, const void *u, void *du, float *dbias, int64_t rows, int C, mdt_stream_t stream);
 
+/* N2  dense (+ GELU) as one tcgen05 GEMM with a fused epilogue     (same reference lines as mdt_gelu_fwd)
+ *   out[M,N] = a[M,K] * w[N,K]^T + bias[N];  act = 1: aux = that (the pre-activation, saved for the backward) and
+ *   out = gelu(aux) -- the activation then costs one extra write instead of a read + write pass over [M,N].
+ *   bf16 row-major; lda / ldw = leading dimensions of a / w in elements; out / aux dense; N % 256 == 0, K % 64 == 0. */
+int mdt_gemm_bias_act(const void *a, int64_t lda, const void *w, int64_t ldw, const void *bias, void *out, void *aux,
+                      int M, int N, int K, int act, mdt_stream_t stream);
+
 /* Self-test of the tcgen05 building blocks (shared-memory descriptor layouts, TMA 128-byte
  * swizzle, TMEM read-back); called by tests/ only.  All operands bf16, row major:
  *   d1[128,128] = a[128,64] * b[128,64]^T          (A and B K-major, both via TMA)

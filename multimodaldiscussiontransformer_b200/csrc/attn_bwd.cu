@@ -282,7 +282,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
                             }
                             const float p = ex2(x + nn[u]);
                             float keepf = 1.f;  // dropout on P: dV takes keep * P / (1 - p_drop), dS = P * (keep * dP / (1 - p_drop) - delta)
-                            if (a.drop.thr16) keepf = drop_keep_one(a.drop, salt, (uint32_t)(q0 + cc * 32 + e), (uint32_t)T, (uint32_t)key) ? a.drop.scale : 0.f;
+                            if (a.drop.thr16) keepf = drop_keep_one(a.drop, salt, (uint32_t)(q0 + cc * 32 + e), (uint32_t)key) ? a.drop.scale : 0.f;
                             const float ds = p * (dp[e] * keepf - dd[u]);
                             st[e] = p * keepf;
                             dp[e] = ds;
@@ -362,7 +362,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
                 for (int u = 0; u < 4; ++u) {
                     const float p = key_ok ? ex2(fmaf(st[i2 + u], kLog2e, nn[u])) : 0.f;
                     float keepf = 1.f;
-                    if (a.drop.thr16) keepf = drop_keep_one(a.drop, salt, (uint32_t)(q0 + cc * 32 + i2 + u), (uint32_t)T, (uint32_t)key) ? a.drop.scale : 0.f;
+                    if (a.drop.thr16) keepf = drop_keep_one(a.drop, salt, (uint32_t)(q0 + cc * 32 + i2 + u), (uint32_t)key) ? a.drop.scale : 0.f;
                     st[i2 + u] = p * keepf;
                     dp[i2 + u] = p * (dp[i2 + u] * keepf - dd[u]);
                 }

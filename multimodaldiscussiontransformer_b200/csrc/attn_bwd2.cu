@@ -302,7 +302,8 @@ __global__ void __launch_bounds__(kB2Threads, 1)
         reg_alloc<152>();
         const int half = tid >> 7;  // which 64 query columns of every tile
         const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
-        const uint32_t salt = drop_salt(a.drop, (uint32_t)(b * a.H + h));
+        const uint32_t salt = drop_salt(a.drop, (uint32_t)(b * a.H + h)), thr32 = a.drop.thr16 << 16;
+        const uint32_t drop_k = drop_tile(salt, (uint32_t)key >> 6, 1u) ^ drop_lane(64u + ((uint32_t)key & 63u));
         const bool warp_keys = __any_sync(0xffffffffu, key_ok);  // a warp whose 32 keys are all masked only writes zeros
         const uint32_t lut_base = smem_u32(ctl.lut);
 
@@ -310,6 +311,7 @@ __global__ void __launch_bounds__(kB2Threads, 1)
             const int q0 = i * kTile;
             const int qvalid = min(kTile, T - q0);
             const bool live = warp_keys && half * 64 < qvalid;   // warp-uniform
+            const uint32_t drop_w = HAS_DROP ? drop_k ^ drop_tile(salt, (uint32_t)(i * 2 + half), 0u) : 0u;  // 64 queries of this half
             float st[64], dp[64];
             mbar_wait(&ctl.sp_full, i & 1);
             tc_fence_after();
@@ -354,7 +356,7 @@ __global__ void __launch_bounds__(kB2Threads, 1)
                             float kf[4];
 #pragma unroll
                             for (int u = 0; u < 4; ++u)
-                                kf[u] = drop_keep_one(a.drop, salt, (uint32_t)(q0 + half * 64 + g * 16 + v4 * 4 + u), (uint32_t)T, (uint32_t)key) ? a.drop.scale : 0.f;
+                                kf[u] = drop_keep_w(drop_w, drop_lane(g * 16 + v4 * 4 + u), thr32) ? a.drop.scale : 0.f;
                             fmul2(y[0], y[1], y[0], y[1], kf[0], kf[1]);
                             fmul2(y[2], y[3], y[2], y[3], kf[2], kf[3]);
                             fadd2(y[0], y[1], y[0], y[1], -__uint_as_float(d4.x), -__uint_as_float(d4.y));

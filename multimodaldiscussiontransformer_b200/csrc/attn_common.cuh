@@ -27,10 +27,16 @@ inline int bias_mode(const void *bias, int bias_dtype, const uint8_t *code) {
 }
 
 // ---- attention dropout (multihead_attention.py:196): the keep mask is a counter hash, never stored.
-//   salt(b,h) = fmix32(seed_lo ^ (b*H+h) * 0x9e3779b1) + seed_hi
-//   hp(q,k)   = mix(salt ^ (q*T + (k & ~1)));   r16 = k odd ? hp & 0xffff : hp >> 16;   keep <=> r16 >= thr16
-// so the forward (a thread walks along k: one hash per two elements) and the backward (a thread owns one key: one
-// hash per element) regenerate the same mask from (seed, b, h, q, k).  thr16 == 0 switches dropout off.
+//   salt(b,h)  = fmix32(seed_lo ^ (b*H+h) * 0x9e3779b1) + seed_hi
+//   tile(t, w) = fmix32(salt ^ (2 t + w) * 0x9e3779b1)            one strong hash per 64 queries (w = 0) / 64 keys (w = 1)
+//   lane(c)    = fmix32((c + 1) * 0x9e3779b1)                      a constant per position inside the 64 (c + 64 for keys)
+//   x(q, k)    = (tile(q >> 6, 0) ^ lane(q & 63) ^ tile(k >> 6, 1) ^ lane(64 + (k & 63))) * 0x9e3779b1
+//   keep <=> x >= thr16 << 16                                      (drop probability thr16 / 65536)
+// The strong hashes cost ~10 integer operations per 64 elements; inside an unrolled loop lane() folds to an immediate, so
+// an element costs xor + multiply + compare + select whether a thread walks along the keys of one query (forward) or
+// along the queries of one key (backward): both regenerate the same mask from (seed, b, h, q, k).  thr16 == 0 switches
+// dropout off.  The packed-sequence kernels (attn_varlen.cu) keep the older pair hash drop_hash below: there both passes
+// walk along keys.
 struct DropArgs {
     uint32_t thr16;   // round(p * 65536)
     float scale;      // 1 / (1 - p)
@@ -44,25 +50,39 @@ inline DropArgs make_drop(float p, uint64_t seed) {
     d.seed_lo = (uint32_t)seed, d.seed_hi = (uint32_t)(seed >> 32);
     return d;
 }
-__device__ __forceinline__ uint32_t drop_salt(const DropArgs &d, uint32_t bh) {
-    uint32_t h = d.seed_lo ^ (bh * 0x9e3779b1u);
+__host__ __device__ constexpr uint32_t drop_fmix(uint32_t h) {
     h ^= h >> 16;
     h *= 0x85ebca6bu;
     h ^= h >> 13;
     h *= 0xc2b2ae35u;
     h ^= h >> 16;
-    return h + d.seed_hi;
+    return h;
 }
-__device__ __forceinline__ uint32_t drop_hash(uint32_t salt, uint32_t e_even) {  // e_even = q*T + (k & ~1)
+__device__ __forceinline__ uint32_t drop_salt(const DropArgs &d, uint32_t bh) {
+    return drop_fmix(d.seed_lo ^ (bh * 0x9e3779b1u)) + d.seed_hi;
+}
+constexpr uint32_t kDropMul = 0x9e3779b1u;
+// which = 0: a tile of 64 queries, 1: a tile of 64 keys
+__device__ __forceinline__ uint32_t drop_tile(uint32_t salt, uint32_t tile, uint32_t which) {
+    return drop_fmix(salt ^ ((2u * tile + which) * kDropMul));
+}
+// c = q & 63 for a query, 64 + (k & 63) for a key; constant-folds when c is a compile-time value
+__host__ __device__ constexpr uint32_t drop_lane(uint32_t c) { return drop_fmix((c + 1u) * kDropMul); }
+// w = the xor of the two tile hashes and of the lane constant of the coordinate the thread owns
+__device__ __forceinline__ bool drop_keep_w(uint32_t w, uint32_t lane_const, uint32_t thr32) {
+    return (w ^ lane_const) * kDropMul >= thr32;
+}
+__device__ __forceinline__ bool drop_keep_one(const DropArgs &d, uint32_t salt, uint32_t q, uint32_t k) {
+    const uint32_t w = drop_tile(salt, q >> 6, 0u) ^ drop_lane(q & 63u) ^ drop_tile(salt, k >> 6, 1u);
+    return drop_keep_w(w, drop_lane(64u + (k & 63u)), d.thr16 << 16);
+}
+// packed-sequence kernels: hp(e) for the element pair (e, e + 1), e even; r16 = high half for e, low half for e + 1
+__device__ __forceinline__ uint32_t drop_hash(uint32_t salt, uint32_t e_even) {
     uint32_t x = (salt ^ e_even) * 0x9e3779b1u;
     x ^= x >> 15;
     x *= 0x85ebca77u;
     x ^= x >> 13;
     return x;
-}
-__device__ __forceinline__ bool drop_keep_one(const DropArgs &d, uint32_t salt, uint32_t q, uint32_t T, uint32_t k) {
-    const uint32_t hp = drop_hash(salt, q * T + (k & ~1u));
-    return ((k & 1u) ? (hp & 0xffffu) : (hp >> 16)) >= d.thr16;
 }
 
 // TMA view of a strided bf16 tensor addressed (b, t, h, c): dims innermost-first {64, T, H, B},

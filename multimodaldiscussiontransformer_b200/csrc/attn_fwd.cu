@@ -201,12 +201,14 @@ __global__ void __launch_bounds__(128, 2)
         }
         l += sum;
         if (a.drop.thr16) {  // dropout on P (multihead_attention.py:196); the row sum above is of the undropped p
-            const uint32_t salt = drop_salt(a.drop, (uint32_t)(b * a.H + h)), row = (uint32_t)q * (uint32_t)T;
+            const uint32_t salt = drop_salt(a.drop, (uint32_t)(b * a.H + h)), thr32 = a.drop.thr16 << 16;
+            const uint32_t wq = drop_tile(salt, (uint32_t)q >> 6, 0u) ^ drop_lane((uint32_t)q & 63u);
 #pragma unroll
-            for (int i = 0; i < 128; i += 2) {
-                const uint32_t hp = drop_hash(salt, row + (uint32_t)(k0 + i));
-                s[i] = (hp >> 16) >= a.drop.thr16 ? s[i] * a.drop.scale : 0.f;
-                s[i + 1] = (hp & 0xffffu) >= a.drop.thr16 ? s[i + 1] * a.drop.scale : 0.f;
+            for (int hk = 0; hk < 2; ++hk) {   // k0 is a multiple of 128: two hash tiles of 64 keys
+                const uint32_t w = wq ^ drop_tile(salt, (uint32_t)(k0 >> 6) + hk, 1u);
+#pragma unroll
+                for (int i = 0; i < 64; ++i)
+                    s[hk * 64 + i] = drop_keep_w(w, drop_lane(64u + i), thr32) ? s[hk * 64 + i] * a.drop.scale : 0.f;
             }
         }
         // ---- P (bf16) -> swizzled K-major A tile: two 64-key halves of 16 KB

@@ -309,13 +309,15 @@ __global__ void __launch_bounds__(kF3Threads, 1)
             if (tid == 0) f3_trace(a, 2 + 12 * n + 0);
             const uint32_t lut_base = smem_u32(ctl.lut[buf]);
             float m_used = neg_inf(), l = 0.f;   // m_used in log2 units (scores are scaled by log2 e on the fly)
-            const uint32_t salt = drop_salt(a.drop, (uint32_t)(it.b * H + it.h)), drop_row = (uint32_t)q * (uint32_t)T;
+            const uint32_t salt = drop_salt(a.drop, (uint32_t)(it.b * H + it.h)), thr32 = a.drop.thr16 << 16;
+            const uint32_t drop_q = HAS_DROP ? drop_tile(salt, (uint32_t)q >> 6, 0u) ^ drop_lane((uint32_t)q & 63u) : 0u;
 
             for (int j = 0; j < nkv; ++j, ++g) {
                 const int s = g & 1;
                 uint32_t kmask[2];
 #pragma unroll
                 for (int c = 0; c < 2; ++c) kmask[c] = ctl.kmask[buf][j * 4 + hf * 2 + c];
+                const uint32_t drop_w = HAS_DROP ? drop_q ^ drop_tile(salt, (uint32_t)(j * 2 + hf), 1u) : 0u;  // 64 keys of this half
                 float sc[64];
                 mbar_wait(&ctl.s_full[t], g & 1);
                 if (tid == 0 && j == 0) f3_trace(a, 2 + 12 * n + 1);
@@ -429,10 +431,9 @@ __global__ void __launch_bounds__(kF3Threads, 1)
                                     x[i] = ex2(x[i]);
                                     x[i + 1] = ex2(x[i + 1]);
                                     fadd2(sum0, sum1, sum0, sum1, x[i], x[i + 1]);   // the row sum is of the undropped p
-                                    if (HAS_DROP) {  // dropout on P (multihead_attention.py:196): keys k, k + 1 share one hash
-                                        const uint32_t hp = drop_hash(salt, drop_row + (uint32_t)(j * kTile + hf * 64 + ch * 8 + i));
-                                        x[i] = (hp >> 16) >= a.drop.thr16 ? x[i] * a.drop.scale : 0.f;
-                                        x[i + 1] = (hp & 0xffffu) >= a.drop.thr16 ? x[i + 1] * a.drop.scale : 0.f;
+                                    if (HAS_DROP) {  // dropout on P (multihead_attention.py:196)
+                                        x[i] = drop_keep_w(drop_w, drop_lane(64u + ch * 8 + i), thr32) ? x[i] * a.drop.scale : 0.f;
+                                        x[i + 1] = drop_keep_w(drop_w, drop_lane(65u + ch * 8 + i), thr32) ? x[i + 1] * a.drop.scale : 0.f;
                                     }
                                     pw[(ch - 4 * c) * 4 + (i >> 1)] = pack_bf16x2(x[i], x[i + 1]);
                                 }

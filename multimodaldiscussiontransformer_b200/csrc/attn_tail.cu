@@ -66,7 +66,7 @@ __global__ void __launch_bounds__(kTailThreads) attn_bwd_tail_k_kernel(const Tai
             if (HAS_CODE) x += s_lut[code];
             const float p0 = sm100::ex2(x);
             float keepf = 1.f;
-            if (a.drop.thr16) keepf = drop_keep_one(a.drop, salt, (uint32_t)q, (uint32_t)T, (uint32_t)k) ? a.drop.scale : 0.f;
+            if (a.drop.thr16) keepf = drop_keep_one(a.drop, salt, (uint32_t)q, (uint32_t)k) ? a.drop.scale : 0.f;
             const float ds = p0 * (dp * keepf - delta);
             const float p = p0 * keepf;  // what dV sees
             if (p0 != 0.f) {

@@ -634,3 +634,23 @@ def linear_qkv(x: torch.Tensor, q_lin, k_lin, v_lin) -> torch.Tensor:
     """``cat([q_lin(x), k_lin(x), v_lin(x)], -1)`` as one GEMM over the fused parameter storage (no per-call ``cat``)."""
     wf, bf = fused_qkv_storage(q_lin, k_lin, v_lin)
     return _Linear3.apply(x, q_lin.weight, k_lin.weight, v_lin.weight, q_lin.bias, k_lin.bias, v_lin.bias, wf, bf)
+
+
+def gemm_bias_act(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], gelu_act: bool = False):
+    """``x @ weight^T + bias`` on this library's tcgen05 GEMM (csrc/gemm.cu); with ``gelu_act`` returns ``(gelu(u), u)``.
+    bf16, ``weight.shape[0] % 256 == 0``, ``x.shape[-1] % 64 == 0``."""
+    lib = _lib.load()
+    _require_cuda(x, weight, bias)
+    x2 = x.reshape(-1, x.shape[-1])
+    if x2.stride(1) != 1 or x2.stride(0) % 8 != 0:
+        x2 = x2.contiguous()
+    w = weight if weight.stride(1) == 1 and weight.stride(0) % 8 == 0 else weight.contiguous()
+    M, K = x2.shape
+    N = w.shape[0]
+    out = torch.empty((M, N), dtype=torch.bfloat16, device=x.device)
+    aux = torch.empty_like(out) if gelu_act else None
+    b = bias.contiguous() if bias is not None else None
+    with torch.cuda.device(x.device):
+        _lib.check(lib.mdt_gemm_bias_act(_lib.ptr(x2), x2.stride(0), _lib.ptr(w), w.stride(0), _lib.ptr(b), _lib.ptr(out), _lib.ptr(aux),
+                                         M, N, K, 1 if gelu_act else 0, _lib.stream()), "mdt_gemm_bias_act")
+    return (out, aux) if gelu_act else out

@@ -291,27 +291,33 @@ def test_backward_T1025(ops):
 _M32 = 0xFFFFFFFF
 
 
-def dropout_keep_mask(seed, p, B, H, T, device="cuda"):
-    """bool [B,H,T,T]: csrc/attn_common.cuh drop_salt / drop_hash / drop_keep_one in 64-bit integer torch ops."""
-    thr = min(65535, int(p * 65536.0 + 0.5))
-    lo, hi = seed & _M32, (seed >> 32) & _M32
-    bh = torch.arange(B * H, dtype=torch.int64, device=device)
-    h = (lo ^ ((bh * 0x9E3779B1) & _M32)) & _M32
+def _fmix(h):
     h = h ^ (h >> 16)
     h = (h * 0x85EBCA6B) & _M32
     h = h ^ (h >> 13)
     h = (h * 0xC2B2AE35) & _M32
-    h = h ^ (h >> 16)
-    salt = ((h + hi) & _M32).view(B * H, 1, 1)
-    q = torch.arange(T, dtype=torch.int64, device=device).view(1, T, 1)
-    k = torch.arange(T, dtype=torch.int64, device=device).view(1, 1, T)
-    e = (q * T + (k & ~1)) & _M32
-    x = ((salt ^ e) * 0x9E3779B1) & _M32
-    x = x ^ (x >> 15)
-    x = (x * 0x85EBCA77) & _M32
-    x = x ^ (x >> 13)
-    r16 = torch.where((k & 1) == 1, x & 0xFFFF, x >> 16)
-    return (r16 >= thr).view(B, H, T, T)
+    return h ^ (h >> 16)
+
+
+def dropout_keep_mask(seed, p, B, H, T, device="cuda"):
+    """bool [B,H,T,T]: csrc/attn_common.cuh drop_salt / drop_tile / drop_lane / drop_keep_w in 64-bit integer torch ops."""
+    thr = min(65535, int(p * 65536.0 + 0.5)) << 16
+    lo, hi = seed & _M32, (seed >> 32) & _M32
+    mul = 0x9E3779B1
+    bh = torch.arange(B * H, dtype=torch.int64, device=device)
+    salt = ((_fmix((lo ^ ((bh * mul) & _M32)) & _M32) + hi) & _M32).view(B * H, 1)
+    t = torch.arange(T, dtype=torch.int64, device=device).view(1, T)
+
+    def tile(which):
+        return _fmix(salt ^ (((2 * (t >> 6) + which) * mul) & _M32))
+
+    def lane(c):
+        return _fmix(((c + 1) * mul) & _M32)
+
+    row = (tile(0) ^ lane(t & 63)).view(B * H, T, 1)
+    col = (tile(1) ^ lane(64 + (t & 63))).view(B * H, 1, T)
+    x = ((row ^ col) * mul) & _M32
+    return (x >= thr).view(B, H, T, T)
 
 
 def reference_dropout(q, k, v, bias, key_pad, keep, p):

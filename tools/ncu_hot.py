@@ -1,14 +1,20 @@
 #!/usr/bin/env python
-"""Top stall sites of an ncu source page: python tools/ncu_hot.py src.csv [N]"""
+"""Top stall sites of an ncu source page: python tools/ncu_hot.py src.csv [N] [section]
+
+A report with several launches holds one table per launch and view (SASS, then source); ``section`` picks one
+(default 0)."""
 import csv, sys
 rows = list(csv.reader(open(sys.argv[1])))
 n = int(sys.argv[2]) if len(sys.argv) > 2 else 25
-hi = next(i for i, r in enumerate(rows) if r and r[0] == "Address")
+sec = int(sys.argv[3]) if len(sys.argv) > 3 else 0
+heads = [i for i, r in enumerate(rows) if r and r[0] in ("Address", "#")]
+hi = heads[sec]
+end = heads[sec + 1] if sec + 1 < len(heads) else len(rows)
 h = rows[hi]
 ix = {k: i for i, k in enumerate(h)}
-body = [r for r in rows[hi + 1:] if len(r) == len(h)]
+body = [r for r in rows[hi + 1:end] if len(r) == len(h)]
 tot = sum(int(r[ix["# Samples"]] or 0) for r in body)
-print("total samples", tot)
+print("sections", len(heads), "total samples", tot)
 stalls = [k for k in h if k.startswith("stall_") and "Not Issued" not in k]
 for pos, r in sorted(enumerate(body), key=lambda t: -int(t[1][ix["# Samples"]] or 0))[:n]:
     s = int(r[ix["# Samples"]] or 0)
