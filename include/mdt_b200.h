@@ -105,6 +105,20 @@ int mdt_collate_graphs(const int32_t *edge_src, const int32_t *edge_dst, const i
                        int32_t *spatial_pos, void *attn_bias, int bias_dtype, int64_t *in_degree,
                        uint8_t *bias_code, int code_pitch, uint8_t *adj_workspace, mdt_stream_t stream);
 
+/* mdt_collate_graphs without a caller-provided workspace, for callers that cannot allocate device memory (CUDA graph
+ * capture, serving loops, harnesses that forbid cudaMalloc).  It has NO counterpart in the reference.
+ * Same arguments, results and errors as mdt_collate_graphs minus adj_workspace: the
+ * [B,N8,N8] adjacency scratch is a file-scope device array of MDT_COLLATE_STATIC_MAX_BYTES inside the library (held by
+ * every GPU that loads it until exit).  B * N8 * N8 beyond that limit is rejected with MDT_EINVAL (e.g. 32 graphs of 512 nodes,
+ * 128 of 256, 2048 of 64 fit).  The call allocates nothing (no cudaMalloc / cudaFree).  All calls share the one array:
+ * the part a call uses is cleared on `stream` first, and calls that overlap on the same GPU (different streams) race --
+ * serialise them. */
+#define MDT_COLLATE_STATIC_MAX_BYTES (8u << 20)
+int mdt_collate_graphs_static(const int32_t *edge_src, const int32_t *edge_dst, const int32_t *edge_offsets,
+                              const int32_t *n_nodes, int B, int N, int spatial_pos_max, int flavour,
+                              int32_t *spatial_pos, void *attn_bias, int bias_dtype, int64_t *in_degree,
+                              uint8_t *bias_code, int code_pitch, mdt_stream_t stream);
+
 /* ------------------------------------------------------------------------------------
  * A5  GraphAttnBias.forward / backward      mDT/src/modules/graphormer_layers.py:86-110
  *   out[b,h,i,j] = 2*attn_bias[b,i,j] + (i>=1 && j>=1 ? table[spatial_pos[b,i-1,j-1], h]

@@ -38,6 +38,8 @@ SIGNATURES = {
     "mdt_gen_edge_input": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "mdt_collate_graphs": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
                                    c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
+    "mdt_collate_graphs_static": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
+                                          c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p]),
     "mdt_attn_bias_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
                                   c_void_p, c_void_p]),
     "mdt_attn_bias_bwd": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
@@ -93,7 +95,7 @@ def load():
 # C-ABI calls made so far (name -> count) and the kernels each one launches: bench.py reports
 # the number of this library's kernel launches inside its timed region from these.
 CALLS: dict = {}
-KERNELS_PER_CALL = {"mdt_apsp_batched": 1, "mdt_gen_edge_input": 1, "mdt_collate_graphs": 2, "mdt_attn_bias_fwd": 1,
+KERNELS_PER_CALL = {"mdt_apsp_batched": 1, "mdt_gen_edge_input": 1, "mdt_collate_graphs": 2, "mdt_collate_graphs_static": 2, "mdt_attn_bias_fwd": 1,
                     "mdt_attn_bias_bwd": 1, "mdt_biased_attn_fwd": 1, "mdt_biased_attn_bwd": 2, "mdt_varlen_attn_plan": 1,
                     "mdt_varlen_attn_fwd": 1, "mdt_varlen_attn_bwd": 1, "mdt_node_feature_fwd": 1,
                     "mdt_node_feature_bwd": 1, "mdt_gather_rows": 1, "mdt_scatter_rows": 1, "mdt_umma_selftest": 1, "mdt_dropout_add_ln_fwd": 1,

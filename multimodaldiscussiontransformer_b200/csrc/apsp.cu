@@ -540,3 +540,48 @@ extern "C" int mdt_collate_graphs(const int32_t *edge_src, const int32_t *edge_d
     p.code_pitch = code_pitch;
     return launch_tile_kernel(p, n8x8, s);
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// mdt_collate_graphs_static: mdt_collate_graphs for callers that cannot allocate device memory (CUDA graph capture, serving
+// loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The [B, N8, N8] byte adjacency scratch lives in a file-scope device array of MDT_COLLATE_STATIC_MAX_BYTES (8 MiB) that every
+// GPU loading the library holds until exit.  All calls share it, so calls that overlap on one GPU (two streams) race; the
+// array keeps the previous call's bytes, and the part a call uses is cleared on the caller's stream before it is filled.
+// In host code `g_static_adj` is only a stand-in for the symbol: the device address comes from cudaGetSymbolAddress, looked
+// up once per device with that device current.
+// ---------------------------------------------------------------------------------------------------------------------
+static __device__ __align__(256) uint8_t g_static_adj[MDT_COLLATE_STATIC_MAX_BYTES];
+
+static int static_adj_address(uint8_t **out) {
+    static uint8_t *cached[64] = {nullptr};   // per device; a racing first call stores the same value twice
+    int dev = 0;
+    MDT_CHECK_CUDA(cudaGetDevice(&dev));
+    MDT_REQUIRE(dev >= 0 && dev < 64, "mdt_collate_graphs_static: device ordinal %d out of range", dev);
+    if (cached[dev] == nullptr) {
+        void *p = nullptr;
+        MDT_CHECK_CUDA(cudaGetSymbolAddress(&p, g_static_adj));
+        MDT_REQUIRE(p != nullptr, "mdt_collate_graphs_static: cudaGetSymbolAddress returned a null address");
+        cached[dev] = static_cast<uint8_t *>(p);
+    }
+    *out = cached[dev];
+    return MDT_OK;
+}
+
+extern "C" int mdt_collate_graphs_static(const int32_t *edge_src, const int32_t *edge_dst, const int32_t *edge_offsets,
+                                         const int32_t *n_nodes, int B, int N, int spatial_pos_max, int flavour,
+                                         int32_t *spatial_pos, void *attn_bias, int bias_dtype, int64_t *in_degree,
+                                         uint8_t *bias_code, int code_pitch, mdt_stream_t stream) {
+    if (int rc = require_sm100()) return rc;
+    MDT_REQUIRE(B >= 1 && N >= 1 && N <= 512, "bad batch shape B=%d N=%d (N <= 512)", B, N);
+    const size_t n8x8 = (size_t)((N + 7) / 8) * 8;
+    const size_t need = (size_t)B * n8x8 * n8x8;
+    MDT_REQUIRE(need <= (size_t)MDT_COLLATE_STATIC_MAX_BYTES,
+                "mdt_collate_graphs_static: B=%d graphs of N=%d nodes need %zu bytes of adjacency scratch, the static array holds %zu "
+                "(use mdt_collate_graphs with a caller-provided workspace)",
+                B, N, need, (size_t)MDT_COLLATE_STATIC_MAX_BYTES);
+    uint8_t *scratch = nullptr;
+    if (int rc = static_adj_address(&scratch)) return rc;
+    // the shared path clears [0, need) on `stream` (cudaMemsetAsync: no allocation) before the edges are scattered into it
+    return mdt_collate_graphs(edge_src, edge_dst, edge_offsets, n_nodes, B, N, spatial_pos_max, flavour, spatial_pos, attn_bias,
+                              bias_dtype, in_degree, bias_code, code_pitch, scratch, stream);
+}
