@@ -258,6 +258,13 @@ int mdt_dropout_add_ln_fwd(const void *x, const void *residual, const void *gamm
 int mdt_dropout_add_ln_bwd(const void *dy, const void *z, const float *mean, const float *rstd, const void *gamma,
                            void *dx, void *dres, float *dgamma, float *dbeta, int64_t rows, int C, float p,
                            uint64_t seed, mdt_stream_t stream);
+/* the same backward with one more accumulated output: dxsum f32 [C] += column sums of the (rounded) tensor written to dx
+ * (to dres when dx is null) -- the bias gradient of the dense layer whose output was x (BertSelfOutput.dense /
+ * BertOutput.dense, graphormer_graph_encoder_layer.py fc2 / out_proj), so that gradient needs no pass of its own.
+ * dxsum may be null (then this is mdt_dropout_add_ln_bwd). */
+int mdt_dropout_add_ln_bwd_colsum(const void *dy, const void *z, const float *mean, const float *rstd, const void *gamma,
+                                  void *dx, void *dres, float *dgamma, float *dbeta, float *dxsum, int64_t rows, int C,
+                                  float p, uint64_t seed, mdt_stream_t stream);
 
 /* ------------------------------------------------------------------------------------
  * N2  GELU of the feed-forward blocks (exact erf form, fp32 arithmetic on bf16 tensors)
@@ -266,6 +273,7 @@ int mdt_dropout_add_ln_bwd(const void *dy, const void *z, const float *mean, con
  *   forward : g = u * Phi(u)                                   u, g bf16 [rows, C], C a multiple of 8
  *   backward: du = dg * (Phi(u) + u phi(u));  dbias[c] += sum_r du[r,c]   (f32 [C], accumulated; NULL to skip) --
  *             the bias gradient of the dense layer in front of the activation, without a further pass over du.
+ *             du may be dg (the gradient is overwritten in place).
  * ------------------------------------------------------------------------------------ */
 int mdt_gelu_fwd(const void *u, void *g, int64_t rows, int C, mdt_stream_t stream);
 int mdt_gelu_bwd(const void *dg, const void *u, void *du, float *dbias, int64_t rows, int C, mdt_stream_t stream);

@@ -35,8 +35,7 @@ inline int bias_mode(const void *bias, int bias_dtype, const uint8_t *code) {
 // The strong hashes cost ~10 integer operations per 64 elements; inside an unrolled loop lane() folds to an immediate, so
 // an element costs xor + multiply + compare + select whether a thread walks along the keys of one query (forward) or
 // along the queries of one key (backward): both regenerate the same mask from (seed, b, h, q, k).  thr16 == 0 switches
-// dropout off.  The packed-sequence kernels (attn_varlen.cu) keep the older pair hash drop_hash below: there both passes
-// walk along keys.
+// dropout off.  The packed-sequence kernels (attn_varlen.cu) use drop_chunk below: there both passes walk along keys.
 struct DropArgs {
     uint32_t thr16;   // round(p * 65536)
     float scale;      // 1 / (1 - p)
@@ -76,13 +75,10 @@ __device__ __forceinline__ bool drop_keep_one(const DropArgs &d, uint32_t salt, 
     const uint32_t w = drop_tile(salt, q >> 6, 0u) ^ drop_lane(q & 63u) ^ drop_tile(salt, k >> 6, 1u);
     return drop_keep_w(w, drop_lane(64u + (k & 63u)), d.thr16 << 16);
 }
-// packed-sequence kernels: hp(e) for the element pair (e, e + 1), e even; r16 = high half for e, low half for e + 1
-__device__ __forceinline__ uint32_t drop_hash(uint32_t salt, uint32_t e_even) {
-    uint32_t x = (salt ^ e_even) * 0x9e3779b1u;
-    x ^= x >> 15;
-    x *= 0x85ebca77u;
-    x ^= x >> 13;
-    return x;
+// packed-sequence kernels (attn_varlen.cu; salt per (head, unit of 128 packed rows), both passes walk along the keys of
+// a row): one strong hash per (row r, 32-key chunk c), then  x = (chunk ^ lane(i)) * 0x9e3779b1  for key 32 c + i
+__device__ __forceinline__ uint32_t drop_chunk(uint32_t salt, uint32_t r, uint32_t c) {
+    return drop_fmix(salt ^ ((r * 4u + c) * kDropMul));
 }
 
 // TMA view of a strided bf16 tensor addressed (b, t, h, c): dims innermost-first {64, T, H, B},

@@ -251,7 +251,7 @@ __global__ void __launch_bounds__(kVlThreads, 2)
         if (warp_live) {
             const float nm = (m == neg_inf()) ? 0.f : -m;
             const float sl2 = a.scale_log2;
-            const uint32_t salt = drop_salt(a.drop, (uint32_t)w);
+            const uint32_t salt = drop_salt(a.drop, (uint32_t)w), thr32 = a.drop.thr16 << 16;
             float sum0 = 0.f, sum1 = 0.f;
 #pragma unroll
             for (int j = 0; j < 2; ++j) {
@@ -265,6 +265,7 @@ __global__ void __launch_bounds__(kVlThreads, 2)
                     continue;
                 }
                 float *xc = x + j * 32;
+                const uint32_t dw = drop_chunk(salt, (uint32_t)r, (uint32_t)c);
 #pragma unroll
                 for (int i = 0; i < 32; i += 2) {   // masked entries are -inf: 2^(-inf) = 0, no select
                     ffma2(xc[i], xc[i + 1], xc[i], xc[i + 1], sl2, sl2, nm, nm);
@@ -272,9 +273,8 @@ __global__ void __launch_bounds__(kVlThreads, 2)
                     xc[i + 1] = ex2(xc[i + 1]);
                     fadd2(sum0, sum1, sum0, sum1, xc[i], xc[i + 1]);   // the row sum is of the undropped p
                     if (a.drop.thr16) {
-                        const uint32_t hp = drop_hash(salt, (uint32_t)(r * 128 + c * 32 + i));
-                        xc[i] = (hp >> 16) >= a.drop.thr16 ? xc[i] * a.drop.scale : 0.f;
-                        xc[i + 1] = (hp & 0xffffu) >= a.drop.thr16 ? xc[i + 1] * a.drop.scale : 0.f;
+                        xc[i] = drop_keep_w(dw, drop_lane(i), thr32) ? xc[i] * a.drop.scale : 0.f;
+                        xc[i + 1] = drop_keep_w(dw, drop_lane(i + 1), thr32) ? xc[i + 1] * a.drop.scale : 0.f;
                     }
                 }
 #pragma unroll
@@ -440,7 +440,7 @@ __global__ void __launch_bounds__(kVlThreads, 2)
         __syncwarp();
         // ---- pass A: delta = rowsum(dO * O) = sum_k keep P dP / (1 - p_drop) over the row's window -- from S and dP alone,
         // no O / dO rows from global memory (their DRAM latency sat on every unit's critical path, and 25 % of the traffic)
-        const uint32_t salt = drop_salt(a.drop, (uint32_t)w);
+        const uint32_t salt = drop_salt(a.drop, (uint32_t)w), thr32 = a.drop.thr16 << 16;
         const float sl2 = a.scale_log2, sc = a.scale;
         float dpart = 0.f;
         if (warp_used) {
@@ -456,14 +456,14 @@ __global__ void __launch_bounds__(kVlThreads, 2)
                 tmem_wait_ld();
                 if (bits != 0u) {
                     float a0 = 0.f, a1 = 0.f;
+                    const uint32_t dw = drop_chunk(salt, (uint32_t)r, (uint32_t)c);
 #pragma unroll
                     for (int i = 0; i < 32; i += 2) {
                         float p0 = (bits >> i) & 1u ? ex2(fmaf(st[i], sl2, nlse)) : 0.f;
                         float p1 = (bits >> (i + 1)) & 1u ? ex2(fmaf(st[i + 1], sl2, nlse)) : 0.f;
                         if (a.drop.thr16) {
-                            const uint32_t hp = drop_hash(salt, (uint32_t)(r * 128 + c * 32 + i));
-                            p0 = (hp >> 16) >= a.drop.thr16 ? p0 * a.drop.scale : 0.f;
-                            p1 = (hp & 0xffffu) >= a.drop.thr16 ? p1 * a.drop.scale : 0.f;
+                            p0 = drop_keep_w(dw, drop_lane(i), thr32) ? p0 * a.drop.scale : 0.f;
+                            p1 = drop_keep_w(dw, drop_lane(i + 1), thr32) ? p1 * a.drop.scale : 0.f;
                         }
                         a0 = fmaf(p0, dp[i], a0);
                         a1 = fmaf(p1, dp[i + 1], a1);
@@ -498,6 +498,7 @@ __global__ void __launch_bounds__(kVlThreads, 2)
                         *reinterpret_cast<uint4 *>(sdS + off) = make_uint4(0, 0, 0, 0);
                     }
                 } else {
+                    const uint32_t dw = drop_chunk(salt, (uint32_t)r, (uint32_t)c);
                     if (bits != 0xffffffffu) {
 #pragma unroll
                         for (int i = 0; i < 32; ++i)
@@ -509,9 +510,8 @@ __global__ void __launch_bounds__(kVlThreads, 2)
                         st[i] = ex2(st[i]);
                         st[i + 1] = ex2(st[i + 1]);
                         if (a.drop.thr16) {
-                            const uint32_t hp = drop_hash(salt, (uint32_t)(r * 128 + c * 32 + i));
-                            const float k0 = (hp >> 16) >= a.drop.thr16 ? a.drop.scale : 0.f;
-                            const float k1 = (hp & 0xffffu) >= a.drop.thr16 ? a.drop.scale : 0.f;
+                            const float k0 = drop_keep_w(dw, drop_lane(i), thr32) ? a.drop.scale : 0.f;
+                            const float k1 = drop_keep_w(dw, drop_lane(i + 1), thr32) ? a.drop.scale : 0.f;
                             ffma2(dp[i], dp[i + 1], dp[i], dp[i + 1], k0 * sc, k1 * sc, nds, nds);
                             fmul2(dp[i], dp[i + 1], dp[i], dp[i + 1], st[i], st[i + 1]);
                             fmul2(st[i], st[i + 1], st[i], st[i + 1], k0, k1);

@@ -74,7 +74,7 @@ __global__ void __launch_bounds__(kTx *kTy) gelu_fwd_kernel(const uint4 *__restr
     }
 }
 
-__global__ void __launch_bounds__(kTx *kTy) gelu_bwd_kernel(const uint4 *__restrict__ dg, const uint4 *__restrict__ u, uint4 *__restrict__ du,
+__global__ void __launch_bounds__(kTx *kTy) gelu_bwd_kernel(const uint4 *dg, const uint4 *__restrict__ u, uint4 *du,
                                                              float *__restrict__ dbias, int64_t rows, int vec_per_row) {
     __shared__ float red[kTy][kTx * 8 + 1];
     const int cx = blockIdx.x * kTx + threadIdx.x;
@@ -83,23 +83,33 @@ __global__ void __launch_bounds__(kTx *kTy) gelu_bwd_kernel(const uint4 *__restr
 #pragma unroll
     for (int i = 0; i < 8; ++i) acc[i] = 0.f;
     if (col_ok) {
-        for (int64_t r = (int64_t)blockIdx.y * kTy + threadIdx.y; r < rows; r += (int64_t)gridDim.y * kTy) {
-            float x[8], d[8];
-            unpack8(__ldg(u + r * vec_per_row + cx), x);
-            unpack8(__ldg(dg + r * vec_per_row + cx), d);
+        const int64_t step = (int64_t)gridDim.y * kTy;
+        // two rows in flight per thread; all four loads are issued before the first store (du may be dg: in-place)
+        for (int64_t r = (int64_t)blockIdx.y * kTy + threadIdx.y; r < rows; r += 2 * step) {
+            const bool two = r + step < rows;
+            const int64_t r1 = two ? r + step : r;
+            const uint4 u0 = __ldg(u + r * vec_per_row + cx), u1 = __ldg(u + r1 * vec_per_row + cx);
+            const uint4 g0 = dg[r * vec_per_row + cx], g1 = dg[r1 * vec_per_row + cx];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                float cdf, e;
-                phi_cdf(x[i], cdf, e);
-                d[i] *= fmaf(x[i] * 0.39894228040143268f, e, cdf);   // Phi(x) + x * phi(x)
-            }
-            const uint4 out = pack8(d);
-            du[r * vec_per_row + cx] = out;
-            if (dbias != nullptr) {   // the sums are of the ROUNDED gradient, the tensor the weight-gradient GEMM reads
-                float q[8];
-                unpack8(out, q);
+            for (int h = 0; h < 2; ++h) {
+                if (h == 1 && !two) break;
+                float x[8], d[8];
+                unpack8(h == 0 ? u0 : u1, x);
+                unpack8(h == 0 ? g0 : g1, d);
 #pragma unroll
-                for (int i = 0; i < 8; ++i) acc[i] += q[i];
+                for (int i = 0; i < 8; ++i) {
+                    float cdf, e;
+                    phi_cdf(x[i], cdf, e);
+                    d[i] *= fmaf(x[i] * 0.39894228040143268f, e, cdf);   // Phi(x) + x * phi(x)
+                }
+                const uint4 out = pack8(d);
+                du[(h == 0 ? r : r1) * vec_per_row + cx] = out;
+                if (dbias != nullptr) {   // the sums are of the ROUNDED gradient, the tensor the weight-gradient GEMM reads
+                    float q[8];
+                    unpack8(out, q);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) acc[i] += q[i];
+                }
             }
         }
     }

@@ -170,6 +170,7 @@ struct BwdArgs {
     const float *mean, *rstd;
     __nv_bfloat16 *dx, *dres;
     float *dgamma, *dbeta;
+    float *dxsum;   // column sums of the (rounded) tensor written to dx, or to dres without dx: the bias gradient of the dense layer in front
     int64_t rows;
     float scale;
     uint32_t thr16;
@@ -194,7 +195,7 @@ constexpr int kBwdThreads = 384;  // 12 warps: 12 / VEC row groups
 constexpr int kBwdStages = 4;
 constexpr int kBwdSmem = kBwdStages * 2 * kBwdThreads * 16;  // 48 KB of dynamic shared memory (6 stages measured no faster)
 
-template <int VEC>
+template <int VEC, bool XSUM>
 __global__ void __launch_bounds__(kBwdThreads, 2) ln_bwd_kernel(const BwdArgs a) {
     constexpr int C = VEC * 256;
     constexpr int kW = kBwdThreads / 32, kGroups = kW / VEC;
@@ -206,10 +207,14 @@ __global__ void __launch_bounds__(kBwdThreads, 2) ln_bwd_kernel(const BwdArgs a)
     const int group = warp / VEC, sub = warp % VEC;  // this lane owns columns [sub * 256 + lane * 8, + 8)
     const int64_t row0 = (int64_t)blockIdx.x * kGroups + group, nrows = (int64_t)gridDim.x * kGroups;
     const int col = sub * 32 + lane;                  // vector index inside the row
-    float g[8], dg[8], db[8];
+    float g[8], dg[8], db[8], xs[XSUM ? 8 : 1];
     unpack8(__ldg(reinterpret_cast<const uint4 *>(a.gamma) + col), g);
 #pragma unroll
     for (int i = 0; i < 8; ++i) dg[i] = db[i] = 0.f;
+    if (XSUM) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) xs[i] = 0.f;
+    }
     auto issue = [&](int64_t row, int st) {
         if (row < a.rows) {
             cp_async16(&stage_mem[st][0][threadIdx.x], reinterpret_cast<const uint4 *>(a.dy + row * C) + col);
@@ -253,22 +258,32 @@ __global__ void __launch_bounds__(kBwdThreads, 2) ln_bwd_kernel(const BwdArgs a)
         float dz[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) dz[i] = (dy[i] - c1 - xh[i] * c2) * rstd;
-        if (a.dres) reinterpret_cast<uint4 *>(a.dres + row * C)[col] = pack8(dz);
+        uint4 packed = pack8(dz);
+        if (a.dres) reinterpret_cast<uint4 *>(a.dres + row * C)[col] = packed;
         if (a.dx) {
-            if (a.thr16) apply_keep(dz, rand4(a.seed, (uint64_t)row * (C / 8) + col), a.thr16, a.scale);
-            reinterpret_cast<uint4 *>(a.dx + row * C)[col] = pack8(dz);
+            if (a.thr16) {
+                apply_keep(dz, rand4(a.seed, (uint64_t)row * (C / 8) + col), a.thr16, a.scale);
+                packed = pack8(dz);
+            }
+            reinterpret_cast<uint4 *>(a.dx + row * C)[col] = packed;
+        }
+        if (XSUM) {   // sums of the rounded values: the tensor the weight-gradient GEMM reads
+            float q[8];
+            unpack8(packed, q);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) xs[i] += q[i];
         }
     }
     cp_async_wait<0>();
     // ---- per-CTA column sums over the row groups (the staging buffers are dead now), then one fp32 atomic per column and CTA
     float(*red)[C] = reinterpret_cast<float(*)[C]>(ln_smem);
 #pragma unroll
-    for (int which = 0; which < 2; ++which) {
+    for (int which = 0; which < (XSUM ? 3 : 2); ++which) {
         __syncthreads();
 #pragma unroll
-        for (int i = 0; i < 8; ++i) red[group][col * 8 + i] = which == 0 ? dg[i] : db[i];
+        for (int i = 0; i < 8; ++i) red[group][col * 8 + i] = which == 0 ? dg[i] : which == 1 ? db[i] : xs[XSUM ? i : 0];
         __syncthreads();
-        float *dst = which == 0 ? a.dgamma : a.dbeta;
+        float *dst = which == 0 ? a.dgamma : which == 1 ? a.dbeta : a.dxsum;
         for (int c = threadIdx.x; c < C; c += kBwdThreads) {
             float s = 0.f;
 #pragma unroll
@@ -283,8 +298,13 @@ static int launch_bwd(const BwdArgs &a, cudaStream_t st) {
     constexpr int kGroups = kBwdThreads / 32 / VEC;
     const int64_t want = (a.rows + kGroups - 1) / kGroups, cap = (int64_t)num_sms() * 2;
     const int grid = (int)(want < cap ? want : cap);
-    MDT_CHECK_CUDA(cudaFuncSetAttribute(ln_bwd_kernel<VEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem));  // per device
-    ln_bwd_kernel<VEC><<<grid, kBwdThreads, kBwdSmem, st>>>(a);
+    if (a.dxsum) {
+        MDT_CHECK_CUDA(cudaFuncSetAttribute(ln_bwd_kernel<VEC, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem));
+        ln_bwd_kernel<VEC, true><<<grid, kBwdThreads, kBwdSmem, st>>>(a);
+    } else {
+        MDT_CHECK_CUDA(cudaFuncSetAttribute(ln_bwd_kernel<VEC, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem));  // per device
+        ln_bwd_kernel<VEC, false><<<grid, kBwdThreads, kBwdSmem, st>>>(a);
+    }
     MDT_CHECK_CUDA(cudaGetLastError());
     return MDT_OK;
 }
@@ -338,6 +358,12 @@ extern "C" int mdt_dropout_add_ln_fwd(const void *x, const void *residual, const
 extern "C" int mdt_dropout_add_ln_bwd(const void *dy, const void *z, const float *mean, const float *rstd, const void *gamma,
                                       void *dx, void *dres, float *dgamma, float *dbeta, int64_t rows, int C, float p,
                                       uint64_t seed, mdt_stream_t stream) {
+    return mdt_dropout_add_ln_bwd_colsum(dy, z, mean, rstd, gamma, dx, dres, dgamma, dbeta, nullptr, rows, C, p, seed, stream);
+}
+
+extern "C" int mdt_dropout_add_ln_bwd_colsum(const void *dy, const void *z, const float *mean, const float *rstd, const void *gamma,
+                                             void *dx, void *dres, float *dgamma, float *dbeta, float *dxsum, int64_t rows, int C,
+                                             float p, uint64_t seed, mdt_stream_t stream) {
     if (int rc = require_sm100()) return rc;
     if (int rc = check_c(C, "mdt_dropout_add_ln_bwd")) return rc;
     MDT_REQUIRE(dy && z && mean && rstd && gamma && dgamma && dbeta, "mdt_dropout_add_ln_bwd: null argument");
@@ -346,7 +372,7 @@ extern "C" int mdt_dropout_add_ln_bwd(const void *dy, const void *z, const float
     if (rows <= 0) return MDT_OK;
     ln::BwdArgs a;
     a.dy = (const __nv_bfloat16 *)dy, a.z = (const __nv_bfloat16 *)z, a.gamma = (const __nv_bfloat16 *)gamma, a.mean = mean, a.rstd = rstd;
-    a.dx = (__nv_bfloat16 *)dx, a.dres = (__nv_bfloat16 *)dres, a.dgamma = dgamma, a.dbeta = dbeta;
+    a.dx = (__nv_bfloat16 *)dx, a.dres = (__nv_bfloat16 *)dres, a.dgamma = dgamma, a.dbeta = dbeta, a.dxsum = dxsum;
     a.rows = rows, a.thr16 = thr16_of(p), a.scale = 1.f / (1.f - p), a.seed = seed;
     cudaStream_t st = as_stream(stream);
     switch (C / 256) {

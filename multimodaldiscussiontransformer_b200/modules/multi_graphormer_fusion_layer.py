@@ -101,6 +101,8 @@ class _SeqLens:
 #: "mdt" = this library's tcgen05 kernels (csrc/attn_varlen.cu); "flash" = flash-attn's varlen entry, kept only as the
 #: A/B comparison of benchmarks/text_attn_probe.py (MDT_TEXT_ATTN=flash) -- never a fallback: "mdt" raises when it cannot run.
 TEXT_ATTN_IMPL = os.environ.get("MDT_TEXT_ATTN", "mdt")
+#: "0" keeps the block as separate autograd nodes (A/B runs); the arithmetic and the kernels are the same
+FUSED_TEXT_LAYER = os.environ.get("MDT_FUSED_TEXT_LAYER", "1") != "0"
 _FLASH = None
 
 
@@ -128,6 +130,16 @@ def packed_bert_layer(layer, x: torch.Tensor, pack) -> torch.Tensor:
     att, sa = layer.attention, layer.attention.self
     H = sa.num_attention_heads
     d = x.shape[-1] // H
+    if (FUSED_TEXT_LAYER and TEXT_ATTN_IMPL == "mdt" and x.is_cuda and x.dtype == torch.bfloat16 and x.dim() == 2 and d == 64
+            and x.shape[-1] in (256, 512, 768, 1024) and getattr(layer.intermediate, "_mdt_exact_gelu", False)
+            and sa.query.bias is not None and torch.is_grad_enabled()):
+        # the whole block as one autograd node (ops.packed_post_ln_layer): no gradient-accumulation adds and no separate
+        # bias-gradient reductions in the backward
+        if pack.max_seqlen > 128:
+            raise RuntimeError(f"packed text attention handles sequences of <= 128 rows, got {pack.max_seqlen}")
+        return ops.packed_post_ln_layer(x, pack.plan, H, sa.dropout.p, att.output.dropout.p, sa.query, sa.key, sa.value,
+                                        att.output.dense, att.output.LayerNorm, layer.intermediate.dense, layer.output.dense,
+                                        layer.output.LayerNorm, layer.training)
     qkv = ops.linear_qkv(x, sa.query, sa.key, sa.value).view(-1, 3, H, d)
     ctx = _varlen_attention(qkv, pack, sa.dropout.p if layer.training else 0.0).reshape(x.shape)
     if x.dtype == torch.bfloat16 and x.shape[-1] in (256, 512, 768, 1024):

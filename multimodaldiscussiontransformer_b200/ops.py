@@ -654,3 +654,142 @@ def gemm_bias_act(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Te
         _lib.check(lib.mdt_gemm_bias_act(_lib.ptr(x2), x2.stride(0), _lib.ptr(w), w.stride(0), _lib.ptr(b), _lib.ptr(out), _lib.ptr(aux),
                                          M, N, K, 1 if gelu_act else 0, _lib.stream()), "mdt_gemm_bias_act")
     return (out, aux) if gelu_act else out
+
+
+# ------------------------------------------------------------------------------------------
+# N2  a whole post-LN transformer block of the fusion layers as ONE autograd node with a hand-written backward
+#     (HF BertLayer called from multi_graphormer_fusion_layer.py:94-98 on packed tokens).
+#     The arithmetic is the kernels above plus cuBLAS GEMMs; what the single node removes is the autograd glue between
+#     them: the two gradient-accumulation adds over [total, C] per block (the residual gradients are accumulated by the
+#     input-gradient GEMMs, beta = 1), the bias-gradient reductions of the two output dense layers (column sums inside the
+#     LayerNorm backward), the GELU gradient written in place, and ~25 autograd nodes per block.
+# ------------------------------------------------------------------------------------------
+def _ln_fwd_raw(x2, r2, w, b, p, seed, eps):
+    lib = _lib.load()
+    rows, C = x2.shape
+    y = torch.empty_like(x2)
+    need_z = r2 is not None or p > 0.0
+    z = torch.empty_like(x2) if need_z else None
+    mean = torch.empty(rows, dtype=torch.float32, device=x2.device)
+    rstd = torch.empty(rows, dtype=torch.float32, device=x2.device)
+    with _timed("ln_fwd", rows, C, (2 if r2 is not None else 0) + (1 if need_z else 0)):
+        _lib.check(lib.mdt_dropout_add_ln_fwd(_lib.ptr(x2), _lib.ptr(r2), _lib.ptr(w), _lib.ptr(b), _lib.ptr(y), _lib.ptr(z),
+                                              _lib.ptr(mean), _lib.ptr(rstd), rows, C, float(p), int(seed), float(eps),
+                                              _lib.stream()), "mdt_dropout_add_ln_fwd")
+    return y, (z if need_z else x2), mean, rstd
+
+
+def _ln_bwd_raw(gy2, z, mean, rstd, w, p, seed):
+    """-> (dx, dres, dgamma f32, dbeta f32, colsum(dx) f32); without dropout dx IS dres (one tensor)."""
+    lib = _lib.load()
+    rows, C = gy2.shape
+    dres = torch.empty_like(gy2)
+    dx = torch.empty_like(gy2) if p > 0.0 else None
+    acc = torch.zeros(3, C, dtype=torch.float32, device=gy2.device)
+    with _timed("ln_bwd", rows, C, 2 if dx is not None else 1):
+        _lib.check(lib.mdt_dropout_add_ln_bwd_colsum(_lib.ptr(gy2), _lib.ptr(z), _lib.ptr(mean), _lib.ptr(rstd), _lib.ptr(w),
+                                                     _lib.ptr(dx), _lib.ptr(dres), _lib.ptr(acc[0]), _lib.ptr(acc[1]),
+                                                     _lib.ptr(acc[2]), rows, C, float(p), int(seed), _lib.stream()),
+                   "mdt_dropout_add_ln_bwd_colsum")
+    return (dx if dx is not None else dres), dres, acc[0], acc[1], acc[2]
+
+
+def _varlen_fwd_raw(qkv, plan, p, seed, scale):
+    lib = _lib.load()
+    total, _, H, _ = qkv.shape
+    out = torch.empty((total, H, 64), dtype=qkv.dtype, device=qkv.device)
+    lse = torch.empty((H, total), dtype=torch.float32, device=qkv.device)
+    rs = qkv.stride(0)
+    with _timed("vl_fwd", total, H, plan.n_seq):
+        _lib.check(lib.mdt_varlen_attn_fwd(_lib.ptr(qkv[:, 0]), _lib.ptr(qkv[:, 1]), _lib.ptr(qkv[:, 2]), rs, rs, rs, total, H,
+                                           plan.n_seq, _lib.ptr(plan.data), _lib.ptr(out), H * 64, _lib.ptr(lse),
+                                           float(scale), float(p), int(seed), _lib.stream()), "mdt_varlen_attn_fwd")
+    return out, lse
+
+
+def _varlen_bwd_raw(qkv, out, lse, plan, go, p, seed, scale):
+    lib = _lib.load()
+    total, _, H, _ = qkv.shape
+    dqkv = torch.empty((total, 3, H, 64), dtype=qkv.dtype, device=qkv.device)  # every row is written (sequences tile [0, total))
+    rs, gs = qkv.stride(0), 3 * H * 64
+    with _timed("vl_bwd", total, H, plan.n_seq):
+        _lib.check(lib.mdt_varlen_attn_bwd(_lib.ptr(qkv[:, 0]), _lib.ptr(qkv[:, 1]), _lib.ptr(qkv[:, 2]), rs, rs, rs,
+                                           _lib.ptr(out), H * 64, _lib.ptr(go), H * 64, _lib.ptr(lse), total, H,
+                                           plan.n_seq, _lib.ptr(plan.data), _lib.ptr(dqkv[:, 0]),
+                                           _lib.ptr(dqkv[:, 1]), _lib.ptr(dqkv[:, 2]), gs, gs, gs, float(scale), float(p),
+                                           int(seed), _lib.stream()), "mdt_varlen_attn_bwd")
+    return dqkv
+
+
+class _PackedPostLNLayer(torch.autograd.Function):
+    """x -> LN1(drop(attn(x Wqkv + b) Wo + bo) + x) = h -> LN2(drop(gelu(h W1 + b1) W2 + b2) + h) on packed rows."""
+
+    @staticmethod
+    def forward(ctx, x, plan, cfg, wq, wk, wv, bq, bk, bv, wf, bf, wo, bo, g1, be1, w1, b1, w2, b2, g2, be2):
+        H, p_attn, p_hid, eps1, eps2, seeds = cfg
+        lib = _lib.load()
+        lin = torch.nn.functional.linear
+        M, C = x.shape
+        with torch.cuda.device(x.device):
+            qkv = lin(x, wf, bf).view(M, 3, H, 64)
+            att, lse = _varlen_fwd_raw(qkv, plan, p_attn, seeds[0], 64 ** -0.5)
+            att = att.view(M, C)
+            h, z1, mean1, rstd1 = _ln_fwd_raw(lin(att, wo, bo), x, g1, be1, p_hid, seeds[1], eps1)
+            u = lin(h, w1, b1)
+            g = torch.empty_like(u)
+            _lib.check(lib.mdt_gelu_fwd(_lib.ptr(u), _lib.ptr(g), u.shape[0], u.shape[1], _lib.stream()), "mdt_gelu_fwd")
+            y, z2, mean2, rstd2 = _ln_fwd_raw(lin(g, w2, b2), h, g2, be2, p_hid, seeds[2], eps2)
+        ctx.save_for_backward(x, qkv, att, lse, z1, mean1, rstd1, h, u, g, z2, mean2, rstd2, wf, wo, g1, w1, w2, g2)
+        ctx.plan, ctx.cfg = plan, cfg
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, qkv, att, lse, z1, mean1, rstd1, h, u, g, z2, mean2, rstd2, wf, wo, g1, w1, w2, g2 = ctx.saved_tensors
+        H, p_attn, p_hid, eps1, eps2, seeds = ctx.cfg
+        lib = _lib.load()
+        M, C = x.shape
+        need = ctx.needs_input_grad   # 0 x | 3-5 wq wk wv | 6-8 bq bk bv | 11 wo 12 bo 13 g1 14 be1 15 w1 16 b1 17 w2 18 b2 19 g2 20 be2
+        bdt = g1.dtype
+        with torch.cuda.device(x.device):
+            dy = dy.contiguous()
+            # ---- feed-forward half (df may alias dh when there is no dropout: df is not read after dh is updated)
+            df, dh, dg2, dbe2, db2 = _ln_bwd_raw(dy, z2, mean2, rstd2, g2, p_hid, seeds[2])
+            dw2 = df.t() @ g if need[17] else None
+            dgl = df @ w2                                              # [M, 4C]; the GELU gradient overwrites it
+            db1 = torch.zeros(u.shape[1], dtype=torch.float32, device=x.device)
+            _lib.check(lib.mdt_gelu_bwd(_lib.ptr(dgl), _lib.ptr(u), _lib.ptr(dgl), _lib.ptr(db1), u.shape[0], u.shape[1],
+                                        _lib.stream()), "mdt_gelu_bwd")
+            dw1 = dgl.t() @ h if need[15] else None
+            dh.addmm_(dgl, w1)                                         # residual gradient + input gradient: one GEMM, beta = 1
+            del dgl, df
+            # ---- attention half
+            da, dx, dg1, dbe1, dbo = _ln_bwd_raw(dh, z1, mean1, rstd1, g1, p_hid, seeds[1])
+            dwo = da.t() @ att if need[11] else None
+            datt = da @ wo
+            dqkv = _varlen_bwd_raw(qkv, att.view(M, H, 64), lse, ctx.plan, datt.view(M, H, 64), p_attn, seeds[0], 64 ** -0.5)
+            dqkv = dqkv.view(M, 3 * C)
+            dwf = dqkv.t() @ x if any(need[3:6]) else None
+            dbf = dqkv.sum(0) if any(need[6:9]) else None
+            if need[0]:
+                dx.addmm_(dqkv, wf)
+            else:
+                dx = None
+        gw = [dwf[i * C:(i + 1) * C] if dwf is not None else None for i in range(3)]
+        gb = [dbf[i * C:(i + 1) * C] if dbf is not None else None for i in range(3)]
+        return (dx, None, None, *gw, *gb, None, None, dwo, dbo.to(bdt), dg1.to(bdt), dbe1.to(bdt), dw1, db1.to(bdt), dw2,
+                db2.to(bdt), dg2.to(bdt), dbe2.to(bdt))
+
+
+def packed_post_ln_layer(x, plan, heads, p_attn, p_hidden, q_lin, k_lin, v_lin, o_lin, ln1, fc1, fc2, ln2, training):
+    """One Hugging Face ``BertLayer`` (post-LN block) on packed rows ``x`` bf16 ``[total, C]`` (``C = 64 * heads`` in
+    {256, 512, 768, 1024}) as a single autograd node; the modules only lend their parameters."""
+    if not (x.is_cuda and x.dtype == torch.bfloat16 and x.dim() == 2 and x.shape[1] == 64 * heads):
+        raise RuntimeError("ops.packed_post_ln_layer: bf16 CUDA rows [total, 64 * heads] (no other path)")
+    wf, bf = fused_qkv_storage(q_lin, k_lin, v_lin)
+    pa, ph = (float(p_attn), float(p_hidden)) if training else (0.0, 0.0)
+    seeds = (next_seed() if pa > 0 else 0, next_seed() if ph > 0 else 0, next_seed() if ph > 0 else 0)
+    cfg = (int(heads), pa, ph, float(ln1.eps), float(ln2.eps), seeds)
+    return _PackedPostLNLayer.apply(x.contiguous(), plan, cfg, q_lin.weight, k_lin.weight, v_lin.weight, q_lin.bias, k_lin.bias,
+                                    v_lin.bias, wf, bf, o_lin.weight, o_lin.bias, ln1.weight, ln1.bias, fc1.weight, fc1.bias,
+                                    fc2.weight, fc2.bias, ln2.weight, ln2.bias)

@@ -117,8 +117,17 @@ def test_varlen_strided_rows_and_scale(ops):
 
 def keep_mask_from_plan(plan, cu, H, seed, p):
     """bool [total, H, 128]: the kernels' counter-hash mask for (packed row, head, tile-local key column)."""
-    thr = min(65535, int(p * 65536.0 + 0.5))
+    thr = min(65535, int(p * 65536.0 + 0.5)) << 16
     lo, hi = seed & _M32, (seed >> 32) & _M32
+    mul = 0x9E3779B1
+
+    def fmix(h):
+        h = h ^ (h >> 16)
+        h = (h * 0x85EBCA6B) & _M32
+        h = h ^ (h >> 13)
+        h = (h * 0xC2B2AE35) & _M32
+        return h ^ (h >> 16)
+
     n_items = plan.n_items()
     firsts = plan.item_first_seq()
     cul = cu.tolist()
@@ -128,21 +137,12 @@ def keep_mask_from_plan(plan, cu, H, seed, p):
     for item in range(n_items):
         r0, r1 = cul[firsts[item]], cul[firsts[item + 1]]
         w = item * H + torch.arange(H, dtype=torch.int64)
-        h = (lo ^ ((w * 0x9E3779B1) & _M32)) & _M32
-        h = h ^ (h >> 16)
-        h = (h * 0x85EBCA6B) & _M32
-        h = h ^ (h >> 13)
-        h = (h * 0xC2B2AE35) & _M32
-        h = h ^ (h >> 16)
-        salt = ((h + hi) & _M32).view(1, H, 1)
+        salt = ((fmix((lo ^ ((w * mul) & _M32)) & _M32) + hi) & _M32).view(1, H, 1)
         r = torch.arange(r1 - r0, dtype=torch.int64).view(-1, 1, 1)
-        e = (r * 128 + (c & ~1)) & _M32
-        x = ((salt ^ e) * 0x9E3779B1) & _M32
-        x = x ^ (x >> 15)
-        x = (x * 0x85EBCA77) & _M32
-        x = x ^ (x >> 13)
-        r16 = torch.where((c & 1) == 1, x & 0xFFFF, x >> 16)
-        keep[r0:r1] = r16 >= thr
+        chunk = fmix(salt ^ (((r * 4 + (c >> 5)) * mul) & _M32))           # drop_chunk(salt, r, c >> 5)
+        lane = fmix((((c & 31) + 1) * mul) & _M32)                          # drop_lane(c & 31)
+        x = ((chunk ^ lane) * mul) & _M32
+        keep[r0:r1] = x >= thr
     return keep
 
 
