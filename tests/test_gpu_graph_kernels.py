@@ -226,6 +226,33 @@ def test_attn_bias_fwd_bwd(ops, B, N, H, dtype):
     np.testing.assert_allclose(virt.grad.cpu().double().numpy(), v64.grad.numpy(), atol=tol * 4, rtol=1e-4)
 
 
+@pytest.mark.parametrize("N,H,hi", [(33, 12, 60), (130, 16, 40), (64, 5, 22)])
+def test_attn_bias_bwd_bf16_wide_indices_and_unaligned_gradient(ops, N, H, hi):
+    """The tensor-core histogram (bf16, H <= 16): spatial indices >= 32 take its atomic side path, and a gradient that is a
+    2-byte-aligned view (planes start at any alignment) is read through aligned vectors; against an fp64 scatter-add."""
+    from multimodaldiscussiontransformer_b200 import _lib
+
+    B, T = 3, N + 1
+    g = torch.Generator().manual_seed(N)
+    sp = torch.randint(0, hi, (B, N, N), generator=g).int().cuda()
+    buf = torch.randn(B * H * T * T + 3, generator=g).bfloat16().cuda()
+    go = buf[3:].view(B, H, T, T)                                   # 6 bytes off the allocation's alignment
+    S = 64
+    g_table = torch.zeros((S, H), dtype=torch.float32, device="cuda")
+    g_virt = torch.zeros((H,), dtype=torch.float32, device="cuda")
+    lib = _lib.load()
+    _lib.check(lib.mdt_attn_bias_bwd(_lib.ptr(go), _lib.ptr(sp), B, H, N, S, _lib.dtype_code(go.dtype), _lib.ptr(g_table),
+                                     _lib.ptr(g_virt), _lib.stream()), "mdt_attn_bias_bwd")
+    g64 = go.double()
+    want = torch.zeros(S, H, dtype=torch.float64, device="cuda")
+    want.index_add_(0, sp.long().reshape(-1), g64[:, :, 1:, 1:].permute(0, 2, 3, 1).reshape(-1, H))
+    want[0] = 0
+    want_v = g64[:, :, 0, :].sum((0, 2)) + g64[:, :, 1:, 0].sum((0, 2))
+    scale = max(1.0, float(want.abs().max()))
+    np.testing.assert_allclose(g_table.double().cpu().numpy(), want.cpu().numpy(), atol=1e-4 * scale, rtol=1e-5)
+    np.testing.assert_allclose(g_virt.double().cpu().numpy(), want_v.cpu().numpy(), atol=1e-4 * scale, rtol=1e-5)
+
+
 def test_attn_bias_golden(ops):
     gold = load("graph_modules.npz")
     inp = cases.graph_module_inputs()
