@@ -51,6 +51,7 @@ def parse_args():
     ap.add_argument("--grad-dtype", default="bf16", choices=["bf16", "fp32"], help="dtype of the all-reduced gradient buckets")
     ap.add_argument("--no-overlap", action="store_true", help="one all-reduce after the backward instead of overlapped buckets")
     ap.add_argument("--fp32-images", action="store_true", help="ship images as fp32 like the reference collator (default bf16)")
+    ap.add_argument("--gaps", default=None, help="diagnostics: write the device idle gaps of one step (torch.profiler) to this JSON and exit")
     ap.add_argument("--fast", action="store_true", help="skip the T=1025 / preprocessing / CPU legs (development runs)")
     ap.add_argument("--prep", action="store_true",
                     help="configs[1] instead of the training step: Floyd-Warshall sweep (16-512 nodes, batch 256) and "
@@ -450,6 +451,32 @@ def run_b200(args):
 
     for i in range(args.warmup):
         step_resident(i)
+    if args.gaps:   # diagnostics: where the device idles inside one step (kernel timeline of torch.profiler), then exit
+        from torch.profiler import ProfilerActivity, profile
+        torch.cuda.synchronize()
+        with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
+            step_resident(args.warmup)
+            torch.cuda.synchronize()
+        ks = sorted(((e.time_range.start, e.time_range.end, e.name) for e in prof.events()
+                     if str(e.device_type).endswith("CUDA") and e.time_range.end > e.time_range.start), key=lambda t: t[0])
+        t0, t1 = ks[0][0], max(k[1] for k in ks)
+        busy_until, idle, gaps = ks[0][0], 0.0, []
+        for a_, b_, n_ in ks:
+            if a_ > busy_until:
+                idle += a_ - busy_until
+                gaps.append((a_ - busy_until, (busy_until - t0) / (t1 - t0), n_[:70]))
+            busy_until = max(busy_until, b_)
+        nseg = 20
+        seg_idle = [0.0] * nseg
+        for g_, pos, _ in gaps:
+            seg_idle[min(nseg - 1, int(pos * nseg))] += g_
+        out = {"step_us": t1 - t0, "idle_us": idle, "idle_frac": idle / (t1 - t0), "kernels": len(ks),
+               "idle_us_by_twentieth_of_step": [round(x) for x in seg_idle],
+               "largest_gaps": [dict(us=round(g_, 1), at=round(pos, 3), next=n_) for g_, pos, n_ in sorted(gaps, reverse=True)[:40]]}
+        with open(args.gaps, "w") as f:
+            json.dump(out, f, indent=1)
+        print(json.dumps({k: v for k, v in out.items() if k != "largest_gaps"}))
+        return
     sampler = ClockSampler(local) if rank == 0 else None
     if sampler:
         sampler.start()

@@ -285,6 +285,13 @@ int mdt_gelu_bwd(const void *dg, const void *u, void *du, float *dbias, int64_t 
 int mdt_gemm_bias_act(const void *a, int64_t lda, const void *w, int64_t ldw, const void *bias, void *out, void *aux,
                       int M, int N, int K, int act, mdt_stream_t stream);
 
+/* N2  weight gradient of a dense layer: out[N, C] += dy[M, N]^T * x[M, C]   (torch: dy.t() @ x; Hugging Face dense layers called
+ *     from mDT/src/modules/multi_graphormer_fusion_layer.py:94-98,138-148, backward pass)
+ *   dy, x bf16 row-major with leading dimensions ldy, ldx (elements, multiples of 8); out fp32 [N, ldo], ACCUMULATED into with
+ *   vector atomics (split-K: the caller zeroes it, or passes a running fp32 gradient); N, C multiples of 256; M < 2^31 rows. */
+int mdt_wgrad_gemm(const void *dy, int64_t ldy, const void *x, int64_t ldx, float *out, int64_t ldo, int64_t M, int N, int C,
+                   mdt_stream_t stream);
+
 /* Self-test of the tcgen05 building blocks (shared-memory descriptor layouts, TMA 128-byte
  * swizzle, TMEM read-back); called by tests/ only.  All operands bf16, row major:
  *   d1[128,128] = a[128,64] * b[128,64]^T          (A and B K-major, both via TMA)

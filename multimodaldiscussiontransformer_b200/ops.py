@@ -21,6 +21,9 @@ from . import _lib
 # (ln_fwd flags: 2 = has residual, 1 = writes z; ln_bwd flags = number of gradient tensors written).
 ATTN_EVENTS = None
 
+#: MDT_OWN_WGRAD=0 sends every weight-gradient GEMM to cuBLAS (A/B runs)
+OWN_WGRAD = __import__("os").environ.get("MDT_OWN_WGRAD", "1") != "0"
+
 
 class _timed:
     def __init__(self, kind, B, H, T):
@@ -721,6 +724,15 @@ def _varlen_bwd_raw(qkv, out, lse, plan, go, p, seed, scale):
     return dqkv
 
 
+def _wgrad(dy2, x2):
+    """``dy2.t() @ x2`` in the parameter dtype: this library's split-K kernel where it wins over cuBLAS (output columns <= 768,
+    both output dimensions multiples of 256; benchmarks/wgrad_microbench.py), cuBLAS otherwise."""
+    N, C = dy2.shape[1], x2.shape[1]
+    if OWN_WGRAD and N % 256 == 0 and C % 256 == 0 and C <= 768 and dy2.shape[0] >= 32768:
+        return wgrad_gemm(dy2, x2).to(dy2.dtype)
+    return dy2.t() @ x2
+
+
 class _PackedPostLNLayer(torch.autograd.Function):
     """x -> LN1(drop(attn(x Wqkv + b) Wo + bo) + x) = h -> LN2(drop(gelu(h W1 + b1) W2 + b2) + h) on packed rows."""
 
@@ -760,16 +772,16 @@ class _PackedPostLNLayer(torch.autograd.Function):
             db1 = torch.zeros(u.shape[1], dtype=torch.float32, device=x.device)
             _lib.check(lib.mdt_gelu_bwd(_lib.ptr(dgl), _lib.ptr(u), _lib.ptr(dgl), _lib.ptr(db1), u.shape[0], u.shape[1],
                                         _lib.stream()), "mdt_gelu_bwd")
-            dw1 = dgl.t() @ h if need[15] else None
+            dw1 = _wgrad(dgl, h) if need[15] else None
             dh.addmm_(dgl, w1)                                         # residual gradient + input gradient: one GEMM, beta = 1
             del dgl, df
             # ---- attention half
             da, dx, dg1, dbe1, dbo = _ln_bwd_raw(dh, z1, mean1, rstd1, g1, p_hid, seeds[1])
-            dwo = da.t() @ att if need[11] else None
+            dwo = _wgrad(da, att) if need[11] else None
             datt = da @ wo
             dqkv = _varlen_bwd_raw(qkv, att.view(M, H, 64), lse, ctx.plan, datt.view(M, H, 64), p_attn, seeds[0], 64 ** -0.5)
             dqkv = dqkv.view(M, 3 * C)
-            dwf = dqkv.t() @ x if any(need[3:6]) else None
+            dwf = _wgrad(dqkv, x) if any(need[3:6]) else None
             dbf = dqkv.sum(0) if any(need[6:9]) else None
             if need[0]:
                 dx.addmm_(dqkv, wf)
@@ -793,3 +805,24 @@ def packed_post_ln_layer(x, plan, heads, p_attn, p_hidden, q_lin, k_lin, v_lin, 
     return _PackedPostLNLayer.apply(x.contiguous(), plan, cfg, q_lin.weight, k_lin.weight, v_lin.weight, q_lin.bias, k_lin.bias,
                                     v_lin.bias, wf, bf, o_lin.weight, o_lin.bias, ln1.weight, ln1.bias, fc1.weight, fc1.bias,
                                     fc2.weight, fc2.bias, ln2.weight, ln2.bias)
+
+
+def wgrad_gemm(dy: torch.Tensor, x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``dy.t() @ x`` for bf16 ``dy [M, N]``, ``x [M, C]`` (N, C multiples of 256) on this library's split-K tcgen05 kernel
+    (csrc/wgrad.cu) -> fp32 ``[N, C]``; with ``out`` the product is accumulated into it."""
+    lib = _lib.load()
+    _require_cuda(dy, x)
+    if dy.dtype != torch.bfloat16 or x.dtype != torch.bfloat16 or dy.dim() != 2 or x.dim() != 2 or dy.shape[0] != x.shape[0]:
+        raise ValueError("wgrad_gemm: bf16 dy [M, N] and x [M, C]")
+    if dy.stride(1) != 1 or dy.stride(0) % 8 != 0 or dy.data_ptr() % 16 != 0:
+        dy = dy.contiguous()
+    if x.stride(1) != 1 or x.stride(0) % 8 != 0 or x.data_ptr() % 16 != 0:
+        x = x.contiguous()
+    M, N = dy.shape
+    C = x.shape[1]
+    if out is None:
+        out = torch.zeros((N, C), dtype=torch.float32, device=dy.device)
+    with torch.cuda.device(dy.device):
+        _lib.check(lib.mdt_wgrad_gemm(_lib.ptr(dy), dy.stride(0), _lib.ptr(x), x.stride(0), _lib.ptr(out), out.stride(0), M, N, C,
+                                      _lib.stream()), "mdt_wgrad_gemm")
+    return out

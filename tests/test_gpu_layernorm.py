@@ -147,3 +147,52 @@ def test_linear_gelu_and_linear_qkv_match_autograd():
     q.bfloat16(), k.bfloat16(), v.bfloat16()
     assert torch.equal(ops.linear_qkv(x, q, k, v), torch.cat([q(x), k(x), v(x)], dim=-1))   # ... and the view is rebuilt
     assert keys_before is not None
+
+
+@pytest.mark.parametrize("M,N,K", [(1, 256, 64), (777, 768, 256), (5000, 3072, 768), (130, 256, 3072)])
+def test_own_gemm_bias_and_gelu_epilogue(M, N, K):
+    """``mdt_gemm_bias_act`` (tcgen05 GEMM, csrc/gemm.cu) against fp32 arithmetic: the bias-only output within one bf16
+    rounding of ``x @ W^T + b`` (<= 2^-8 relative, the test measures bit equality with cuBLAS on most shapes), the GELU
+    epilogue against ``gelu(round_bf16(u))`` with the pre-activation returned as second output; ragged M (masked last tile),
+    a non-contiguous x (row stride > K)."""
+    from multimodaldiscussiontransformer_b200 import ops
+
+    g = torch.Generator(device="cuda").manual_seed(M + N)
+    wide = torch.randn(M, K + 8, device="cuda", generator=g).bfloat16()
+    x = wide[:, :K]                                                   # row stride K + 8
+    w = (torch.randn(N, K, device="cuda", generator=g) * K ** -0.5).bfloat16()
+    b = torch.randn(N, device="cuda", generator=g).bfloat16()
+    u_ref = x.float() @ w.float().t() + b.float()
+    u = ops.gemm_bias_act(x, w, b)
+    assert u.shape == (M, N) and u.dtype == torch.bfloat16
+    err = (u.float() - u_ref).abs()
+    assert bool((err <= 2 ** -8 * u_ref.abs() + 1e-3).all()), float(err.max())
+    act, pre = ops.gemm_bias_act(x, w, b, gelu_act=True)
+    assert torch.equal(pre, u)
+    want = torch.nn.functional.gelu(u.float())
+    assert float((act.float() - want).abs().max()) <= 2 ** -8 * float(want.abs().max()) + 1e-3
+    with pytest.raises(RuntimeError):
+        ops.gemm_bias_act(x, w[:100], b[:100])                        # N must be a multiple of 256
+
+
+@pytest.mark.parametrize("M,N,C", [(1, 256, 256), (63, 256, 512), (4128, 768, 768), (50001, 2304, 768), (9000, 256, 1024)])
+def test_own_weight_gradient_gemm(M, N, C):
+    """``mdt_wgrad_gemm`` (split-K tcgen05, both operands read MN-major): ``dy.t() @ x`` against fp64, <= 2e-5 of the largest
+    entry (fp32 accumulation and output; cuBLAS's bf16 result is 3e-3 away); ragged M (zero-filled last row block), strided
+    operands, accumulation into an existing fp32 buffer."""
+    from multimodaldiscussiontransformer_b200 import ops
+
+    g = torch.Generator(device="cuda").manual_seed(M + N + C)
+    wide = torch.randn(M, N + C + 16, device="cuda", generator=g).bfloat16()
+    dy, x = wide[:, :N], wide[:, N + 16:]                           # row stride N + C + 16: views, no copies
+    want = dy.double().t() @ x.double()
+    got = ops.wgrad_gemm(dy, x)
+    assert got.dtype == torch.float32 and got.shape == (N, C)
+    scale = float(want.abs().max())
+    assert float((got.double() - want).abs().max()) <= 2e-5 * scale
+    base = torch.randn(N, C, device="cuda", generator=g)
+    acc = base.clone()
+    ops.wgrad_gemm(dy, x, out=acc)
+    assert float((acc.double() - base.double() - want).abs().max()) <= 2e-5 * scale + 1e-5
+    with pytest.raises(RuntimeError):
+        ops.wgrad_gemm(dy[:, :200], x)                                 # N must be a multiple of 256
