@@ -261,10 +261,20 @@ int mdt_dropout_add_ln_bwd(const void *dy, const void *z, const float *mean, con
 /* the same backward with one more accumulated output: dxsum f32 [C] += column sums of the (rounded) tensor written to dx
  * (to dres when dx is null) -- the bias gradient of the dense layer whose output was x (BertSelfOutput.dense /
  * BertOutput.dense, graphormer_graph_encoder_layer.py fc2 / out_proj), so that gradient needs no pass of its own.
- * dxsum may be null (then this is mdt_dropout_add_ln_bwd). */
+ * dadd (bf16 [rows, C], may be null) is added to d z before it is written to dres and masked into dx: the gradient of a
+ * residual connection that joins at z (the pre-LN blocks of the ViT: d x = d(residual path) + LayerNorm-path gradient) needs
+ * no add pass of its own.  dxsum and dadd null: this is mdt_dropout_add_ln_bwd. */
 int mdt_dropout_add_ln_bwd_colsum(const void *dy, const void *z, const float *mean, const float *rstd, const void *gamma,
-                                  void *dx, void *dres, float *dgamma, float *dbeta, float *dxsum, int64_t rows, int C,
-                                  float p, uint64_t seed, mdt_stream_t stream);
+                                  const void *dadd, void *dx, void *dres, float *dgamma, float *dbeta, float *dxsum,
+                                  int64_t rows, int C, float p, uint64_t seed, mdt_stream_t stream);
+/* y = dropout_p(x) + residual (residual may be null) without a LayerNorm behind it -- the second residual of a pre-LN block
+ * (Hugging Face ViTOutput, called from mDT/src/modules/multi_graphormer_fusion_layer.py:73-100) -- and its backward
+ * dx = keep * dy / (1 - p) (dx may be null) with dxsum f32 [C] += column sums of the rounded dx (the bias gradient of the
+ * dense layer that produced x; may be null).  bf16 [rows, C], C a multiple of 8; same counter-hash mask as the LayerNorm
+ * entries (a function of seed and element index, never stored). */
+int mdt_dropout_add_fwd(const void *x, const void *residual, void *y, int64_t rows, int C, float p, uint64_t seed,
+                        mdt_stream_t stream);
+int mdt_dropout_bwd(const void *dy, void *dx, float *dxsum, int64_t rows, int C, float p, uint64_t seed, mdt_stream_t stream);
 
 /* ------------------------------------------------------------------------------------
  * N2  GELU of the feed-forward blocks (exact erf form, fp32 arithmetic on bf16 tensors)

@@ -67,7 +67,9 @@ SIGNATURES = {
     "mdt_dropout_add_ln_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                        c_int64, c_int, c_float, c_uint64, c_void_p]),
     "mdt_dropout_add_ln_bwd_colsum": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
-                                              c_void_p, c_void_p, c_int64, c_int, c_float, c_uint64, c_void_p]),
+                                              c_void_p, c_void_p, c_void_p, c_int64, c_int, c_float, c_uint64, c_void_p]),
+    "mdt_dropout_add_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_float, c_uint64, c_void_p]),
+    "mdt_dropout_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_float, c_uint64, c_void_p]),
     "mdt_gelu_fwd": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p]),
     "mdt_gelu_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
     "mdt_gemm_bias_act": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),

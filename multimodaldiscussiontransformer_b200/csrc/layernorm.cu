@@ -167,6 +167,7 @@ __global__ void __launch_bounds__(kThreads) ln_fwd_kernel(const FwdArgs a) {
 
 struct BwdArgs {
     const __nv_bfloat16 *dy, *z, *gamma;
+    const __nv_bfloat16 *dadd;   // optional [rows, C]: added to dz before it is written / masked (a residual gradient that joins here)
     const float *mean, *rstd;
     __nv_bfloat16 *dx, *dres;
     float *dgamma, *dbeta;
@@ -227,6 +228,8 @@ __global__ void __launch_bounds__(kBwdThreads, 2) ln_bwd_kernel(const BwdArgs a)
     int st = 0, par = 0;
     for (int64_t row = row0; row < a.rows; row += nrows, st = st + 1 == kBwdStages ? 0 : st + 1, par ^= 1) {
         const float mean = a.mean[row], rstd = a.rstd[row];
+        uint4 addv = make_uint4(0, 0, 0, 0);
+        if (a.dadd) addv = ldg_stream(reinterpret_cast<const uint4 *>(a.dadd + row * C) + col);   // in flight under the row sums
         issue(row + (kBwdStages - 1) * nrows, st == 0 ? kBwdStages - 1 : st - 1);
         cp_async_wait<kBwdStages - 1>();  // this row's copies have landed
         float dy[8], z[8], xh[8];
@@ -258,6 +261,12 @@ __global__ void __launch_bounds__(kBwdThreads, 2) ln_bwd_kernel(const BwdArgs a)
         float dz[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) dz[i] = (dy[i] - c1 - xh[i] * c2) * rstd;
+        if (a.dadd) {
+            float ad[8];
+            unpack8(addv, ad);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) dz[i] += ad[i];
+        }
         uint4 packed = pack8(dz);
         if (a.dres) reinterpret_cast<uint4 *>(a.dres + row * C)[col] = packed;
         if (a.dx) {
@@ -309,6 +318,94 @@ static int launch_bwd(const BwdArgs &a, cudaStream_t st) {
     return MDT_OK;
 }
 
+// ---- y = dropout_p(x) + residual without a LayerNorm behind it (the second residual of a pre-LN block: Hugging Face ViTOutput),
+// and its backward dx = keep * dy / (1 - p) with the column sums of the rounded dx (= the bias gradient of the dense layer
+// that produced x).  Same keep mask as the LayerNorm kernels: rand4(seed, row * C / 8 + vector).  Threads own one 16-byte
+// vector column and walk down the rows, two rows in flight.
+constexpr int kDaTx = 32, kDaTy = 8;
+
+__global__ void __launch_bounds__(kDaTx *kDaTy)
+    dropout_add_fwd_kernel(const uint4 *__restrict__ x, const uint4 *__restrict__ res, uint4 *__restrict__ y, int64_t rows, int vec_per_row,
+                           uint32_t thr16, float scale, uint64_t seed) {
+    const int cx = blockIdx.x * kDaTx + threadIdx.x;
+    if (cx >= vec_per_row) return;
+    const int64_t step = (int64_t)gridDim.y * kDaTy;
+    for (int64_t r = (int64_t)blockIdx.y * kDaTy + threadIdx.y; r < rows; r += 2 * step) {
+        const bool two = r + step < rows;
+        const int64_t r1 = two ? r + step : r;
+        const uint4 x0 = ldg_stream(x + r * vec_per_row + cx), x1 = ldg_stream(x + r1 * vec_per_row + cx);
+        uint4 q0 = make_uint4(0, 0, 0, 0), q1 = q0;
+        if (res) q0 = ldg_stream(res + r * vec_per_row + cx), q1 = ldg_stream(res + r1 * vec_per_row + cx);
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            if (h == 1 && !two) break;
+            const int64_t rr = h == 0 ? r : r1;
+            float v[8], w[8];
+            unpack8(h == 0 ? x0 : x1, v);
+            unpack8(h == 0 ? q0 : q1, w);
+            if (thr16) apply_keep(v, rand4(seed, (uint64_t)rr * vec_per_row + cx), thr16, scale);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] += w[i];
+            y[rr * vec_per_row + cx] = pack8(v);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kDaTx *kDaTy)
+    dropout_bwd_kernel(const uint4 *__restrict__ dy, uint4 *__restrict__ dx, float *__restrict__ dxsum, int64_t rows, int vec_per_row,
+                       uint32_t thr16, float scale, uint64_t seed) {
+    __shared__ float red[kDaTy][kDaTx * 8 + 1];
+    const int cx = blockIdx.x * kDaTx + threadIdx.x;
+    float acc[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+    if (cx < vec_per_row) {
+        const int64_t step = (int64_t)gridDim.y * kDaTy;
+        for (int64_t r = (int64_t)blockIdx.y * kDaTy + threadIdx.y; r < rows; r += 2 * step) {
+            const bool two = r + step < rows;
+            const int64_t r1 = two ? r + step : r;
+            const uint4 g0 = ldg_stream(dy + r * vec_per_row + cx), g1 = ldg_stream(dy + r1 * vec_per_row + cx);
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                if (h == 1 && !two) break;
+                const int64_t rr = h == 0 ? r : r1;
+                float v[8];
+                unpack8(h == 0 ? g0 : g1, v);
+                if (thr16) apply_keep(v, rand4(seed, (uint64_t)rr * vec_per_row + cx), thr16, scale);
+                const uint4 out = pack8(v);
+                if (dx) dx[rr * vec_per_row + cx] = out;
+                if (dxsum) {
+                    float q[8];
+                    unpack8(out, q);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) acc[i] += q[i];
+                }
+            }
+        }
+    }
+    if (dxsum == nullptr) return;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) red[threadIdx.y][threadIdx.x * 8 + i] = acc[i];
+    __syncthreads();
+    const int t = threadIdx.y * kDaTx + threadIdx.x;
+    const int colo = blockIdx.x * kDaTx * 8 + t;
+    if (colo < vec_per_row * 8) {
+        float sum = 0.f;
+#pragma unroll
+        for (int yy = 0; yy < kDaTy; ++yy) sum += red[yy][t];
+        atomicAdd(dxsum + colo, sum);
+    }
+}
+
+static dim3 da_grid(int64_t rows, int vec_per_row) {
+    const int gx = (vec_per_row + kDaTx - 1) / kDaTx;
+    int64_t gy = ((int64_t)num_sms() * 8 + gx - 1) / gx;
+    const int64_t need = (rows + kDaTy - 1) / kDaTy;
+    if (gy > need) gy = need;
+    if (gy < 1) gy = 1;
+    return dim3((unsigned)gx, (unsigned)gy);
+}
+
 inline int grid_for(int64_t rows) {
     const int64_t want = (rows + kWarps - 1) / kWarps;
     const int64_t cap = (int64_t)num_sms() * 4;
@@ -358,12 +455,12 @@ extern "C" int mdt_dropout_add_ln_fwd(const void *x, const void *residual, const
 extern "C" int mdt_dropout_add_ln_bwd(const void *dy, const void *z, const float *mean, const float *rstd, const void *gamma,
                                       void *dx, void *dres, float *dgamma, float *dbeta, int64_t rows, int C, float p,
                                       uint64_t seed, mdt_stream_t stream) {
-    return mdt_dropout_add_ln_bwd_colsum(dy, z, mean, rstd, gamma, dx, dres, dgamma, dbeta, nullptr, rows, C, p, seed, stream);
+    return mdt_dropout_add_ln_bwd_colsum(dy, z, mean, rstd, gamma, nullptr, dx, dres, dgamma, dbeta, nullptr, rows, C, p, seed, stream);
 }
 
 extern "C" int mdt_dropout_add_ln_bwd_colsum(const void *dy, const void *z, const float *mean, const float *rstd, const void *gamma,
-                                             void *dx, void *dres, float *dgamma, float *dbeta, float *dxsum, int64_t rows, int C,
-                                             float p, uint64_t seed, mdt_stream_t stream) {
+                                             const void *dadd, void *dx, void *dres, float *dgamma, float *dbeta, float *dxsum,
+                                             int64_t rows, int C, float p, uint64_t seed, mdt_stream_t stream) {
     if (int rc = require_sm100()) return rc;
     if (int rc = check_c(C, "mdt_dropout_add_ln_bwd")) return rc;
     MDT_REQUIRE(dy && z && mean && rstd && gamma && dgamma && dbeta, "mdt_dropout_add_ln_bwd: null argument");
@@ -373,6 +470,7 @@ extern "C" int mdt_dropout_add_ln_bwd_colsum(const void *dy, const void *z, cons
     ln::BwdArgs a;
     a.dy = (const __nv_bfloat16 *)dy, a.z = (const __nv_bfloat16 *)z, a.gamma = (const __nv_bfloat16 *)gamma, a.mean = mean, a.rstd = rstd;
     a.dx = (__nv_bfloat16 *)dx, a.dres = (__nv_bfloat16 *)dres, a.dgamma = dgamma, a.dbeta = dbeta, a.dxsum = dxsum;
+    a.dadd = (const __nv_bfloat16 *)dadd;
     a.rows = rows, a.thr16 = thr16_of(p), a.scale = 1.f / (1.f - p), a.seed = seed;
     cudaStream_t st = as_stream(stream);
     switch (C / 256) {
@@ -381,4 +479,30 @@ extern "C" int mdt_dropout_add_ln_bwd_colsum(const void *dy, const void *z, cons
         case 3: return ln::launch_bwd<3>(a, st);
         default: return ln::launch_bwd<4>(a, st);
     }
+}
+
+extern "C" int mdt_dropout_add_fwd(const void *x, const void *residual, void *y, int64_t rows, int C, float p, uint64_t seed,
+                                   mdt_stream_t stream) {
+    if (int rc = require_sm100()) return rc;
+    MDT_REQUIRE(x && y && rows >= 0 && C >= 8 && C % 8 == 0, "mdt_dropout_add_fwd: x, y non-null, C a multiple of 8");
+    MDT_REQUIRE(p >= 0.f && p < 1.f, "mdt_dropout_add_fwd: p must be in [0, 1)");
+    MDT_REQUIRE((((uintptr_t)x | (uintptr_t)residual | (uintptr_t)y) & 15) == 0, "mdt_dropout_add_fwd: buffers must be 16-byte aligned");
+    if (rows == 0) return MDT_OK;
+    ln::dropout_add_fwd_kernel<<<ln::da_grid(rows, C / 8), dim3(ln::kDaTx, ln::kDaTy), 0, as_stream(stream)>>>(
+        (const uint4 *)x, (const uint4 *)residual, (uint4 *)y, rows, C / 8, thr16_of(p), 1.f / (1.f - p), seed);
+    MDT_CHECK_CUDA(cudaGetLastError());
+    return MDT_OK;
+}
+
+extern "C" int mdt_dropout_bwd(const void *dy, void *dx, float *dxsum, int64_t rows, int C, float p, uint64_t seed,
+                               mdt_stream_t stream) {
+    if (int rc = require_sm100()) return rc;
+    MDT_REQUIRE(dy && (dx || dxsum) && rows >= 0 && C >= 8 && C % 8 == 0, "mdt_dropout_bwd: dy and one of dx / dxsum, C a multiple of 8");
+    MDT_REQUIRE(p >= 0.f && p < 1.f, "mdt_dropout_bwd: p must be in [0, 1)");
+    MDT_REQUIRE((((uintptr_t)dy | (uintptr_t)dx) & 15) == 0, "mdt_dropout_bwd: buffers must be 16-byte aligned");
+    if (rows == 0) return MDT_OK;
+    ln::dropout_bwd_kernel<<<ln::da_grid(rows, C / 8), dim3(ln::kDaTx, ln::kDaTy), 0, as_stream(stream)>>>(
+        (const uint4 *)dy, (uint4 *)dx, dxsum, rows, C / 8, thr16_of(p), 1.f / (1.f - p), seed);
+    MDT_CHECK_CUDA(cudaGetLastError());
+    return MDT_OK;
 }

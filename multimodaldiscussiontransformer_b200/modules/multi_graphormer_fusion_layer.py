@@ -103,6 +103,7 @@ class _SeqLens:
 TEXT_ATTN_IMPL = os.environ.get("MDT_TEXT_ATTN", "mdt")
 #: "0" keeps the block as separate autograd nodes (A/B runs); the arithmetic and the kernels are the same
 FUSED_TEXT_LAYER = os.environ.get("MDT_FUSED_TEXT_LAYER", "1") != "0"
+FUSED_VIT_LAYER = os.environ.get("MDT_FUSED_VIT_LAYER", "1") != "0"
 _FLASH = None
 
 
@@ -279,6 +280,17 @@ class GraphFusionLayer(nn.Module):
         return _first(self.bert_encoder(hidden_states, attention_mask))
 
     def vit_forward(self, hidden_states):
+        v = self.vit_encoder
+        sa = getattr(getattr(v, "attention", None), "attention", None)
+        if (FUSED_VIT_LAYER and VIT_ATTN_IMPL == "mdt" and sa is not None and hidden_states.is_cuda
+                and hidden_states.dtype == torch.bfloat16 and hidden_states.dim() == 3 and torch.is_grad_enabled()
+                and hidden_states.shape[-1] in (256, 512, 768, 1024) and hidden_states.shape[-1] == 64 * sa.num_attention_heads
+                and getattr(v.intermediate, "_mdt_exact_gelu", False) and sa.query.bias is not None
+                and type(v).__name__ == "ViTLayer"):
+            # the whole pre-LN block as one autograd node (ops.vit_pre_ln_layer)
+            return ops.vit_pre_ln_layer(hidden_states, sa.num_attention_heads, sa.dropout_prob, v.output.dropout.p,
+                                        v.layernorm_before, sa.query, sa.key, sa.value, v.attention.output.dense,
+                                        v.layernorm_after, v.intermediate.dense, v.output.dense, v.training)
         return _first(self.vit_encoder(hidden_states))
 
     def forward(self, bert_hidden_states, vit_hidden_states, bottle_neck, bert_attention_mask=None, x_image_indexes=None):

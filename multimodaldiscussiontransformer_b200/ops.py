@@ -295,7 +295,8 @@ class _BiasedAttention(torch.autograd.Function):
         lib = _lib.load()
         B, T, H, _ = q.shape
         go = _check_bthd("grad_out", grad_out)
-        dq, dk, dv = _empty_like_layout(q), _empty_like_layout(q), _empty_like_layout(q)
+        views = getattr(ctx, "grad_views", None)   # a caller that wants dq / dk / dv inside one [B, T, 3, H, 64] buffer
+        dq, dk, dv = views if views is not None else (_empty_like_layout(q), _empty_like_layout(q), _empty_like_layout(q))
         dq_accum = torch.zeros((B, H, T, 64), dtype=torch.float32, device=q.device)
         delta = torch.empty((B, H, T), dtype=torch.float32, device=q.device)
         g_bias = torch.empty_like(bias) if (bias is not None and ctx.needs_input_grad[3]) else None
@@ -682,8 +683,8 @@ def _ln_fwd_raw(x2, r2, w, b, p, seed, eps):
     return y, (z if need_z else x2), mean, rstd
 
 
-def _ln_bwd_raw(gy2, z, mean, rstd, w, p, seed):
-    """-> (dx, dres, dgamma f32, dbeta f32, colsum(dx) f32); without dropout dx IS dres (one tensor)."""
+def _ln_bwd_raw(gy2, z, mean, rstd, w, p, seed, dadd=None):
+    """-> (dx, dres, dgamma f32, dbeta f32, colsum(dx) f32); without dropout dx IS dres (one tensor).  ``dadd`` joins d z."""
     lib = _lib.load()
     rows, C = gy2.shape
     dres = torch.empty_like(gy2)
@@ -691,7 +692,7 @@ def _ln_bwd_raw(gy2, z, mean, rstd, w, p, seed):
     acc = torch.zeros(3, C, dtype=torch.float32, device=gy2.device)
     with _timed("ln_bwd", rows, C, 2 if dx is not None else 1):
         _lib.check(lib.mdt_dropout_add_ln_bwd_colsum(_lib.ptr(gy2), _lib.ptr(z), _lib.ptr(mean), _lib.ptr(rstd), _lib.ptr(w),
-                                                     _lib.ptr(dx), _lib.ptr(dres), _lib.ptr(acc[0]), _lib.ptr(acc[1]),
+                                                     _lib.ptr(dadd), _lib.ptr(dx), _lib.ptr(dres), _lib.ptr(acc[0]), _lib.ptr(acc[1]),
                                                      _lib.ptr(acc[2]), rows, C, float(p), int(seed), _lib.stream()),
                    "mdt_dropout_add_ln_bwd_colsum")
     return (dx if dx is not None else dres), dres, acc[0], acc[1], acc[2]
@@ -826,3 +827,120 @@ def wgrad_gemm(dy: torch.Tensor, x: torch.Tensor, out: Optional[torch.Tensor] = 
         _lib.check(lib.mdt_wgrad_gemm(_lib.ptr(dy), dy.stride(0), _lib.ptr(x), x.stride(0), _lib.ptr(out), out.stride(0), M, N, C,
                                       _lib.stream()), "mdt_wgrad_gemm")
     return out
+
+
+# ------------------------------------------------------------------------------------------
+# N2  a whole pre-LN transformer block (Hugging Face ViTLayer, called from multi_graphormer_fusion_layer.py:73-100) as ONE
+#     autograd node:  x2 = x + drop(Wo attn(LN1(x)));  y = x2 + drop(W2 gelu(W1 LN2(x2)))
+#     What the single node removes from the step: the two residual adds and the two gradient-accumulation adds over
+#     [rows, C] per block (LN2 is fused with the first dropout + add, the gradients join inside the LayerNorm backward through
+#     its `dadd` input), five bias-gradient reductions, the separate dropout / masked-scale kernels and ~30 autograd nodes.
+# ------------------------------------------------------------------------------------------
+class _Ctx:
+    """Stand-in for an autograd context: lets the static forward / backward of another Function be called directly."""
+    needs_input_grad = (True,) * 16
+
+    def save_for_backward(self, *t):
+        self.saved_tensors = t
+
+
+def _dropout_add_raw(x2, r2, p, seed):
+    lib = _lib.load()
+    y = torch.empty_like(x2)
+    _lib.check(lib.mdt_dropout_add_fwd(_lib.ptr(x2), _lib.ptr(r2), _lib.ptr(y), x2.shape[0], x2.shape[1], float(p), int(seed),
+                                       _lib.stream()), "mdt_dropout_add_fwd")
+    return y
+
+
+def _dropout_bwd_raw(dy2, p, seed, want_dx=True):
+    """-> (dx (dy itself when p == 0), colsum(dx) f32)"""
+    lib = _lib.load()
+    dx = torch.empty_like(dy2) if (want_dx and p > 0.0) else None
+    xsum = torch.zeros(dy2.shape[1], dtype=torch.float32, device=dy2.device)
+    _lib.check(lib.mdt_dropout_bwd(_lib.ptr(dy2), _lib.ptr(dx), _lib.ptr(xsum), dy2.shape[0], dy2.shape[1], float(p), int(seed),
+                                   _lib.stream()), "mdt_dropout_bwd")
+    return (dx if dx is not None else dy2), xsum
+
+
+class _VitPreLNLayer(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, cfg, wq, wk, wv, bq, bk, bv, wf, bf, wo, bo, g1, be1, w1, b1, w2, b2, g2, be2):
+        H, p_attn, p_hid, eps1, eps2, seeds = cfg
+        lib = _lib.load()
+        lin = torch.nn.functional.linear
+        Bn, T, C = x.shape
+        x2d = x.reshape(Bn * T, C)
+        with torch.cuda.device(x.device):
+            h1, _, mean1, rstd1 = _ln_fwd_raw(x2d, None, g1, be1, 0.0, 0, eps1)
+            qkv = lin(h1, wf, bf).view(Bn, T, 3, H, 64)
+            qkv[:, :, 0].mul_(64 ** -0.5)                      # the kernels take q pre-scaled (multihead_attention.py:137)
+            actx = _Ctx()
+            att = _BiasedAttention.forward(actx, qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2], None, None, None, None, p_attn, seeds[0])
+            att2 = att.reshape(Bn * T, C)
+            # first residual fused with LN2: z2 = drop(o) + x is the block's inner state, h2 = LN2(z2)
+            h2, z2, mean2, rstd2 = _ln_fwd_raw(lin(att2, wo, bo), x2d, g2, be2, p_hid, seeds[1], eps2)
+            u = lin(h2, w1, b1)
+            g = torch.empty_like(u)
+            _lib.check(lib.mdt_gelu_fwd(_lib.ptr(u), _lib.ptr(g), u.shape[0], u.shape[1], _lib.stream()), "mdt_gelu_fwd")
+            y = _dropout_add_raw(lin(g, w2, b2), z2, p_hid, seeds[2])
+        ctx.save_for_backward(x2d, h1, mean1, rstd1, att2, z2, mean2, rstd2, h2, u, g, wf, wo, g1, w1, w2, g2, *actx.saved_tensors[:5])
+        ctx.cfg, ctx.shape = cfg, (Bn, T, C)
+        return y.view(Bn, T, C)
+
+    @staticmethod
+    def backward(ctx, dy):
+        (x2d, h1, mean1, rstd1, att2, z2, mean2, rstd2, h2, u, g, wf, wo, g1, w1, w2, g2, q, k, v, aout, lse) = ctx.saved_tensors
+        H, p_attn, p_hid, eps1, eps2, seeds = ctx.cfg
+        Bn, T, C = ctx.shape
+        lib = _lib.load()
+        need = ctx.needs_input_grad   # 0 x | 2-4 wq wk wv | 5-7 bq bk bv | 10 wo 11 bo 12 g1 13 be1 14 w1 15 b1 16 w2 17 b2 18 g2 19 be2
+        bdt = g1.dtype
+        with torch.cuda.device(dy.device):
+            dy2 = dy.reshape(Bn * T, C).contiguous()
+            # ---- feed-forward half: y = drop(f) + z2
+            df, db2 = _dropout_bwd_raw(dy2, p_hid, seeds[2])
+            dw2 = _wgrad(df, g) if need[16] else None
+            dgl = df @ w2
+            del df
+            db1 = torch.zeros(u.shape[1], dtype=torch.float32, device=dy.device)
+            _lib.check(lib.mdt_gelu_bwd(_lib.ptr(dgl), _lib.ptr(u), _lib.ptr(dgl), _lib.ptr(db1), u.shape[0], u.shape[1],
+                                        _lib.stream()), "mdt_gelu_bwd")
+            dw1 = _wgrad(dgl, h2) if need[14] else None
+            dh2 = dgl @ w1
+            del dgl
+            # LN2 backward; the direct path of the second residual (dy) joins d z2 inside the kernel
+            do, dz2, dg2, dbe2, dbo = _ln_bwd_raw(dh2, z2, mean2, rstd2, g2, p_hid, seeds[1], dadd=dy2)
+            # ---- attention half: z2 = drop(o) + x
+            dwo = _wgrad(do, att2) if need[10] else None
+            datt = (do @ wo).view(Bn, T, H, 64)
+            actx = _Ctx()
+            actx.saved_tensors = (q, k, v, aout, lse, None, None, None, None)
+            actx.pitch, actx.drop = 0, (p_attn, seeds[0])
+            dqkv = torch.empty((Bn, T, 3, H, 64), dtype=dy.dtype, device=dy.device)
+            actx.grad_views = (dqkv[:, :, 0], dqkv[:, :, 1], dqkv[:, :, 2])
+            _BiasedAttention.backward(actx, datt)
+            dqkv[:, :, 0].mul_(64 ** -0.5)
+            dqkv = dqkv.view(Bn * T, 3 * C)
+            dwf = _wgrad(dqkv, h1) if any(need[2:5]) else None
+            dbf = dqkv.sum(0) if any(need[5:8]) else None
+            dh1 = dqkv @ wf
+            # LN1 backward (no dropout, no residual inside LN1: z = x); d z2 (the first residual's direct path) joins here
+            dx, _, dg1, dbe1, _ = _ln_bwd_raw(dh1, x2d, mean1, rstd1, g1, 0.0, 0, dadd=dz2)
+        gw = [dwf[i * C:(i + 1) * C] if dwf is not None else None for i in range(3)]
+        gb = [dbf[i * C:(i + 1) * C] if dbf is not None else None for i in range(3)]
+        return (dx.view(Bn, T, C) if need[0] else None, None, *gw, *gb, None, None, dwo, dbo.to(bdt), dg1.to(bdt), dbe1.to(bdt), dw1,
+                db1.to(bdt), dw2, db2.to(bdt), dg2.to(bdt), dbe2.to(bdt))
+
+
+def vit_pre_ln_layer(x, heads, p_attn, p_hidden, ln1, q_lin, k_lin, v_lin, o_lin, ln2, fc1, fc2, training):
+    """One Hugging Face ``ViTLayer`` (pre-LN block) on ``x`` bf16 ``[B, T, C]`` (``C = 64 * heads`` in {256, 512, 768, 1024})
+    as a single autograd node; the modules only lend their parameters."""
+    if not (x.is_cuda and x.dtype == torch.bfloat16 and x.dim() == 3 and x.shape[2] == 64 * heads):
+        raise RuntimeError("ops.vit_pre_ln_layer: bf16 CUDA [B, T, 64 * heads] (no other path)")
+    wf, bf = fused_qkv_storage(q_lin, k_lin, v_lin)
+    pa, ph = (float(p_attn), float(p_hidden)) if training else (0.0, 0.0)
+    seeds = (next_seed() if pa > 0 else 0, next_seed() if ph > 0 else 0, next_seed() if ph > 0 else 0)
+    cfg = (int(heads), pa, ph, float(ln1.eps), float(ln2.eps), seeds)
+    return _VitPreLNLayer.apply(x.contiguous(), cfg, q_lin.weight, k_lin.weight, v_lin.weight, q_lin.bias, k_lin.bias, v_lin.bias,
+                                wf, bf, o_lin.weight, o_lin.bias, ln1.weight, ln1.bias, fc1.weight, fc1.bias, fc2.weight,
+                                fc2.bias, ln2.weight, ln2.bias)

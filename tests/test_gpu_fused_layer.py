@@ -120,3 +120,130 @@ def test_fused_layer_matches_hugging_face_fp32():
             assert float(g[k].float().abs().max()) <= 2e-2
             continue
         assert rel(g[k], g_ref[k]) <= 3e-2, (k, rel(g[k], g_ref[k]))
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# pre-LN block (Hugging Face ViTLayer) as one autograd node: ops.vit_pre_ln_layer
+# ---------------------------------------------------------------------------------------------------------------------
+def make_vit_layer(p_hidden, p_attn, C=768, seed=0):
+    from transformers import ViTConfig
+    from transformers.models.vit.modeling_vit import ViTLayer
+
+    from multimodaldiscussiontransformer_b200.modules.multi_graphormer_fusion_layer import use_fused_intermediates
+
+    torch.manual_seed(seed)
+    cfg = ViTConfig(hidden_size=C, num_attention_heads=C // 64, intermediate_size=4 * C, hidden_dropout_prob=p_hidden,
+                    attention_probs_dropout_prob=p_attn)
+    cfg._attn_implementation = "eager"
+    layer = ViTLayer(cfg)
+    for n, p in layer.named_parameters():
+        if n.endswith("bias"):
+            torch.nn.init.normal_(p, std=0.05)
+        if "layernorm" in n and n.endswith("weight"):
+            torch.nn.init.normal_(p, mean=1.0, std=0.1)
+    return use_fused_intermediates(layer)
+
+
+def vit_call(layer, x):
+    from multimodaldiscussiontransformer_b200 import ops
+
+    sa = layer.attention.attention
+    return ops.vit_pre_ln_layer(x, sa.num_attention_heads, sa.dropout_prob, layer.output.dropout.p, layer.layernorm_before,
+                                sa.query, sa.key, sa.value, layer.attention.output.dense, layer.layernorm_after,
+                                layer.intermediate.dense, layer.output.dense, layer.training)
+
+
+def vit_reference(layer, x, go, keep_attn=None, p_attn=0.0, m1=None, m2=None):
+    """The block in fp32 torch with explicit masks (``keep_attn`` bool [B,H,T,T]; ``m1`` / ``m2`` = keep / (1 - p) [B*T, C])."""
+    import torch.nn.functional as F
+
+    ref = make_vit_layer(0.0, 0.0, C=x.shape[-1]).cuda().float()
+    ref.load_state_dict({k: v.float() for k, v in layer.state_dict().items()})
+    sa = ref.attention.attention
+    B, T, C = x.shape
+    H = sa.num_attention_heads
+    xr = x.detach().float().requires_grad_(True)
+    h1 = ref.layernorm_before(xr)
+    q, k, v = (m(h1).view(B, T, H, 64).transpose(1, 2) for m in (sa.query, sa.key, sa.value))
+    pr = torch.softmax(q @ k.transpose(-1, -2) * 64 ** -0.5, dim=-1)
+    if keep_attn is not None:
+        pr = pr * keep_attn.float() / (1.0 - p_attn)
+    att = (pr @ v).transpose(1, 2).reshape(B, T, C)
+    o = ref.attention.output.dense(att)
+    z2 = (o if m1 is None else o * m1.view(B, T, C)) + xr
+    f = ref.output.dense(F.gelu(ref.intermediate.dense(ref.layernorm_after(z2))))
+    y = (f if m2 is None else f * m2.view(B, T, C)) + z2
+    y.backward(go.float())
+    return y.detach(), xr.grad, {n: p.grad for n, p in ref.named_parameters()}
+
+
+def check_vit(got, want, tol_out, tol_grad):
+    y, dx, g = got
+    y_ref, dx_ref, g_ref = want
+    assert float((y.float() - y_ref).abs().max()) <= tol_out * max(1.0, float(y_ref.abs().max()))
+    assert rel(dx, dx_ref) <= tol_grad, ("dx", rel(dx, dx_ref))
+    for k_ in g_ref:
+        if k_.endswith("key.bias"):                 # exact gradient 0 (softmax is invariant to a key bias)
+            assert float(g[k_].float().abs().max()) <= 5e-2
+            continue
+        assert rel(g[k_], g_ref[k_]) <= tol_grad, (k_, rel(g[k_], g_ref[k_]))
+
+
+def run_vit(layer, x, go, seed):
+    torch.manual_seed(seed)
+    xi = x.detach().clone().requires_grad_(True)
+    layer.zero_grad(set_to_none=True)
+    y = vit_call(layer, xi)
+    y.backward(go)
+    return y.detach(), xi.grad.detach(), {n: p.grad.detach().clone() for n, p in layer.named_parameters()}
+
+
+@pytest.mark.parametrize("B,T,C", [(3, 201, 768), (2, 64, 256), (5, 130, 512)])
+def test_fused_vit_layer_matches_fp32_formula_without_dropout(B, T, C):
+    """bf16 kernels vs the fp32 block: output <= 2e-2 of the largest entry, gradients <= 3e-2 relative Frobenius."""
+    layer = make_vit_layer(0.0, 0.0, C=C).cuda().bfloat16().train()
+    g = torch.Generator().manual_seed(B * T)
+    x = torch.randn(B, T, C, generator=g).bfloat16().cuda()
+    go = torch.randn(B, T, C, generator=g).bfloat16().cuda()
+    check_vit(run_vit(layer, x, go, 1), vit_reference(layer, x, go), 2e-2, 3e-2)
+
+
+def test_fused_vit_layer_with_dropout_against_the_same_masks():
+    """Dropout 0.3 (hidden) / 0.2 (attention): the reference applies the very masks the kernels generate -- the attention mask
+    restated in torch (tests/test_gpu_attention.py), the two hidden masks read back from ``mdt_dropout_add_fwd`` on ones --
+    so every dropout site and its backward is checked, not just the statistics."""
+    from test_gpu_attention import dropout_keep_mask
+
+    from multimodaldiscussiontransformer_b200 import _lib, ops
+
+    B, T, C, ph, pa = 3, 201, 768, 0.3, 0.2
+    layer = make_vit_layer(ph, pa, C=C).cuda().bfloat16().train()
+    g = torch.Generator().manual_seed(7)
+    x = torch.randn(B, T, C, generator=g).bfloat16().cuda()
+    go = torch.randn(B, T, C, generator=g).bfloat16().cuda()
+    torch.manual_seed(99)
+    seeds = [ops.next_seed() for _ in range(3)]                       # the order vit_pre_ln_layer draws them in
+    lib = _lib.load()
+    ones = torch.ones(B * T, C, dtype=torch.bfloat16, device="cuda")
+    masks = []
+    for s_ in seeds[1:]:
+        m = torch.empty_like(ones)
+        _lib.check(lib.mdt_dropout_add_fwd(_lib.ptr(ones), None, _lib.ptr(m), B * T, C, ph, s_, _lib.stream()), "mdt_dropout_add_fwd")
+        masks.append(m.float())
+        assert abs(float((m > 0).float().mean()) - (1 - ph)) < 1e-2
+    keep = dropout_keep_mask(seeds[0], pa, B, C // 64, T)
+    got = run_vit(layer, x, go, 99)
+    want = vit_reference(layer, x, go, keep_attn=keep, p_attn=pa, m1=masks[0], m2=masks[1])
+    check_vit(got, want, 2e-2, 3e-2)
+
+
+def test_fusion_layer_routes_vit_through_the_single_node():
+    from multimodaldiscussiontransformer_b200 import _lib
+    from multimodaldiscussiontransformer_b200.modules.multi_graphormer_fusion_layer import GraphFusionLayer
+
+    fl = GraphFusionLayer(make_layer(0.0), make_vit_layer(0.1, 0.1), 4).cuda().bfloat16().train()
+    x = torch.randn(2, 201, 768, device="cuda").bfloat16().requires_grad_(True)
+    before = _lib.CALLS.get("mdt_dropout_bwd", 0)
+    fl.vit_forward(x).sum().backward()
+    assert _lib.CALLS.get("mdt_dropout_bwd", 0) == before + 1
+    assert x.grad is not None and bool(torch.isfinite(x.grad).all())
