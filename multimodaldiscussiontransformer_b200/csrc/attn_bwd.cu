@@ -549,7 +549,10 @@ extern "C" int mdt_biased_attn_bwd(const void *q, const void *k, const void *v, 
     const bool bwd2 = use_bwd2 && (mode == kBiasNone || (mode == kBiasCode && code_t != nullptr));
     // The tail-key split pays off for the one-role kernel only: with bwd2 the almost empty key tile of T = 128 k + r is a CTA
     // whose dead warps skip the arithmetic (T = 129: 62 us without the split, 71 us with it and its two helper launches).
-    const int Tmain = tail_split(T, !bwd2 && (mode == kBiasCode || mode == kBiasNone));
+    // ... up to ~6 key tiles.  From T = 768 on the split wins (T = 1025: 884 -> 826 us; T = 513: 285 -> 281; T = 257: 138 -> 142):
+    // the one-key tile costs a ninth of the main kernel there.  MDT_ATTN_TAIL_FROM overrides the threshold (A/B runs).
+    static const int tail_from = []() { const char *e = getenv("MDT_ATTN_TAIL_FROM"); return e ? atoi(e) : 768; }();
+    const int Tmain = tail_split(T, (!bwd2 || T >= tail_from) && (mode == kBiasCode || mode == kBiasNone));
     if (!bwd2 || Tmain < T) {  // delta = rowsum(dO * O)
         const int64_t rows = (int64_t)B * H * T;
         const int threads = 256, rows_per_block = threads / 8;

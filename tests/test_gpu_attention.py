@@ -210,7 +210,7 @@ def run_backward(ops, q, k, v, bias=None, code=None, lut=None, key_pad=None, see
     return got, want
 
 
-@pytest.mark.parametrize("T", [1, 7, 64, 65, 128, 129, 130, 136, 200, 257, 264, 513])
+@pytest.mark.parametrize("T", [1, 7, 64, 65, 128, 129, 130, 136, 200, 257, 264, 513, 769, 775])   # >= 768: tail-key split with bwd2
 @pytest.mark.parametrize("mode", ["none", "f32", "bf16", "code"])
 def test_backward_modes(ops, T, mode):
     B, H = (2, 2) if T > 300 else (3, 4)
@@ -330,7 +330,7 @@ def reference_dropout(q, k, v, bias, key_pad, keep, p):
     return torch.einsum("bhts,bshd->bthd", pr, v.float())
 
 
-@pytest.mark.parametrize("T", [64, 129, 200, 385])
+@pytest.mark.parametrize("T", [64, 129, 200, 385, 770])
 @pytest.mark.parametrize("mode", ["none", "bf16", "code"])
 def test_attention_dropout_forward_backward(ops, T, mode):
     """Forward and gradients with dropout_p = 0.3 against the fp32 formula using the very same mask; T = 64 runs the
