@@ -133,7 +133,7 @@ def packed_bert_layer(layer, x: torch.Tensor, pack) -> torch.Tensor:
     d = x.shape[-1] // H
     if (FUSED_TEXT_LAYER and TEXT_ATTN_IMPL == "mdt" and x.is_cuda and x.dtype == torch.bfloat16 and x.dim() == 2 and d == 64
             and x.shape[-1] in (256, 512, 768, 1024) and getattr(layer.intermediate, "_mdt_exact_gelu", False)
-            and sa.query.bias is not None and torch.is_grad_enabled()):
+            and sa.query.bias is not None):
         # the whole block as one autograd node (ops.packed_post_ln_layer): no gradient-accumulation adds and no separate
         # bias-gradient reductions in the backward
         if pack.max_seqlen > 128:
@@ -253,6 +253,30 @@ def use_fused_intermediates(module: nn.Module) -> nn.Module:
     return module
 
 
+class FusedViTLayer(nn.Module):
+    """Hugging Face ``ViTLayer`` (same parameters and state-dict keys) whose bf16 CUDA forward is the single autograd node
+    ``ops.vit_pre_ln_layer``; anything else (fp32 parity runs, ``MDT_FUSED_VIT_LAYER=0``) takes Hugging Face's forward."""
+
+    def forward(self, hidden_states, *args, **kwargs):
+        sa = self.attention.attention
+        if (FUSED_VIT_LAYER and VIT_ATTN_IMPL == "mdt" and hidden_states.is_cuda and hidden_states.dtype == torch.bfloat16
+                and hidden_states.dim() == 3 and hidden_states.shape[-1] in (256, 512, 768, 1024)
+                and hidden_states.shape[-1] == 64 * sa.num_attention_heads and sa.query.bias is not None
+                and getattr(self.intermediate, "_mdt_exact_gelu", False) and not args and not kwargs):
+            return ops.vit_pre_ln_layer(hidden_states, sa.num_attention_heads, sa.dropout_prob, self.output.dropout.p,
+                                        self.layernorm_before, sa.query, sa.key, sa.value, self.attention.output.dense,
+                                        self.layernorm_after, self.intermediate.dense, self.output.dense, self.training)
+        return super().forward(hidden_states, *args, **kwargs)
+
+
+def use_fused_vit_layers(module: nn.Module) -> nn.Module:
+    """Re-class every Hugging Face ``ViTLayer`` at or below ``module``."""
+    for m in module.modules():
+        if type(m).__name__ == "ViTLayer":
+            m.__class__ = type("FusedViTLayer_", (FusedViTLayer, type(m)), {})
+    return module
+
+
 def use_fused_layer_norms(module: nn.Module) -> nn.Module:
     """Re-class every plain ``nn.LayerNorm`` below ``module`` (the ViT blocks are pre-LN: no residual to fuse)."""
     for m in module.modules():
@@ -265,7 +289,7 @@ class GraphFusionLayer(nn.Module):
     def __init__(self, bert_layer, vit_layer, num_bottle_neck_tokens: int, use_projection: bool = False) -> None:
         super().__init__()
         self.bert_encoder = use_fused_intermediates(bert_layer)
-        self.vit_encoder = use_fused_intermediates(use_mdt_attention(use_fused_layer_norms(vit_layer)))
+        self.vit_encoder = use_fused_vit_layers(use_fused_intermediates(use_mdt_attention(use_fused_layer_norms(vit_layer))))
         self.gradient_checkpointing = False
         self.num_bottle_neck_tokens = num_bottle_neck_tokens
         if use_projection:  # constructed, never applied (multi_graphormer_fusion_layer.py:22-27)
@@ -280,17 +304,6 @@ class GraphFusionLayer(nn.Module):
         return _first(self.bert_encoder(hidden_states, attention_mask))
 
     def vit_forward(self, hidden_states):
-        v = self.vit_encoder
-        sa = getattr(getattr(v, "attention", None), "attention", None)
-        if (FUSED_VIT_LAYER and VIT_ATTN_IMPL == "mdt" and sa is not None and hidden_states.is_cuda
-                and hidden_states.dtype == torch.bfloat16 and hidden_states.dim() == 3 and torch.is_grad_enabled()
-                and hidden_states.shape[-1] in (256, 512, 768, 1024) and hidden_states.shape[-1] == 64 * sa.num_attention_heads
-                and getattr(v.intermediate, "_mdt_exact_gelu", False) and sa.query.bias is not None
-                and type(v).__name__ == "ViTLayer"):
-            # the whole pre-LN block as one autograd node (ops.vit_pre_ln_layer)
-            return ops.vit_pre_ln_layer(hidden_states, sa.num_attention_heads, sa.dropout_prob, v.output.dropout.p,
-                                        v.layernorm_before, sa.query, sa.key, sa.value, v.attention.output.dense,
-                                        v.layernorm_after, v.intermediate.dense, v.output.dense, v.training)
         return _first(self.vit_encoder(hidden_states))
 
     def forward(self, bert_hidden_states, vit_hidden_states, bottle_neck, bert_attention_mask=None, x_image_indexes=None):
