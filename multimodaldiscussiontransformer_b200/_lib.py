@@ -101,7 +101,7 @@ def load():
 # the number of this library's kernel launches inside its timed region from these.
 CALLS: dict = {}
 KERNELS_PER_CALL = {"mdt_apsp_batched": 1, "mdt_gen_edge_input": 1, "mdt_collate_graphs": 2, "mdt_collate_graphs_static": 2, "mdt_attn_bias_fwd": 1,
-                    "mdt_attn_bias_bwd": 1, "mdt_biased_attn_fwd": 1, "mdt_biased_attn_bwd": 2, "mdt_varlen_attn_plan": 1,
+                    "mdt_attn_bias_bwd": 1, "mdt_biased_attn_fwd": 1, "mdt_biased_attn_bwd": 2, "mdt_varlen_attn_plan": 2,
                     "mdt_varlen_attn_fwd": 1, "mdt_varlen_attn_bwd": 1, "mdt_node_feature_fwd": 1,
                     "mdt_node_feature_bwd": 1, "mdt_gather_rows": 1, "mdt_scatter_rows": 1, "mdt_umma_selftest": 1, "mdt_dropout_add_ln_fwd": 1,
                     "mdt_dropout_add_ln_bwd": 1}

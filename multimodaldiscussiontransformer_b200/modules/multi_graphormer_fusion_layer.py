@@ -327,7 +327,7 @@ class GraphFusionLayer(nn.Module):
         (re)written from ``bottle_neck`` and read back after the BERT layer."""
         nb = self.num_bottle_neck_tokens
         C = x_packed.shape[-1]
-        x_packed = packed_bert_layer(self.bert_encoder, x_packed.index_copy(0, pack.bn_rows, bottle_neck.reshape(-1, C)), pack)
+        x_packed = packed_bert_layer(self.bert_encoder, ops.replace_rows(x_packed, pack.bn_rows, bottle_neck.reshape(-1, C)), pack)
         bottle_neck_output = x_packed.index_select(0, pack.bn_rows).view(-1, nb, C)
         if vit_hidden_states is not None:
             rows = image_rows(x_image_indexes)

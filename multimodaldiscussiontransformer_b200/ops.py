@@ -872,8 +872,12 @@ class _VitPreLNLayer(torch.autograd.Function):
         x2d = x.reshape(Bn * T, C)
         with torch.cuda.device(x.device):
             h1, _, mean1, rstd1 = _ln_fwd_raw(x2d, None, g1, be1, 0.0, 0, eps1)
-            qkv = lin(h1, wf, bf).view(Bn, T, 3, H, 64)
-            qkv[:, :, 0].mul_(64 ** -0.5)                      # the kernels take q pre-scaled (multihead_attention.py:137)
+            # the kernels take q pre-scaled by d^-0.5 = 1/8 (multihead_attention.py:137): scale the q rows of the fused weight
+            # (0.6 M elements, exact in bf16) instead of the activations (63 M)
+            ws, bs = wf.clone(), bf.clone()
+            ws[:C].mul_(0.125)
+            bs[:C].mul_(0.125)
+            qkv = lin(h1, ws, bs).view(Bn, T, 3, H, 64)
             actx = _Ctx()
             att = _BiasedAttention.forward(actx, qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2], None, None, None, None, p_attn, seeds[0])
             att2 = att.reshape(Bn * T, C)
@@ -883,7 +887,7 @@ class _VitPreLNLayer(torch.autograd.Function):
             g = torch.empty_like(u)
             _lib.check(lib.mdt_gelu_fwd(_lib.ptr(u), _lib.ptr(g), u.shape[0], u.shape[1], _lib.stream()), "mdt_gelu_fwd")
             y = _dropout_add_raw(lin(g, w2, b2), z2, p_hid, seeds[2])
-        ctx.save_for_backward(x2d, h1, mean1, rstd1, att2, z2, mean2, rstd2, h2, u, g, wf, wo, g1, w1, w2, g2, *actx.saved_tensors[:5])
+        ctx.save_for_backward(x2d, h1, mean1, rstd1, att2, z2, mean2, rstd2, h2, u, g, ws, wo, g1, w1, w2, g2, *actx.saved_tensors[:5])
         ctx.cfg, ctx.shape = cfg, (Bn, T, C)
         return y.view(Bn, T, C)
 
@@ -919,10 +923,13 @@ class _VitPreLNLayer(torch.autograd.Function):
             dqkv = torch.empty((Bn, T, 3, H, 64), dtype=dy.dtype, device=dy.device)
             actx.grad_views = (dqkv[:, :, 0], dqkv[:, :, 1], dqkv[:, :, 2])
             _BiasedAttention.backward(actx, datt)
-            dqkv[:, :, 0].mul_(64 ** -0.5)
-            dqkv = dqkv.view(Bn * T, 3 * C)
+            dqkv = dqkv.view(Bn * T, 3 * C)      # gradient w.r.t. [q / 8 | k | v]: wf here is the weight with its q rows / 8
             dwf = _wgrad(dqkv, h1) if any(need[2:5]) else None
             dbf = dqkv.sum(0) if any(need[5:8]) else None
+            if dwf is not None:
+                dwf[:C].mul_(0.125)
+            if dbf is not None:
+                dbf[:C].mul_(0.125)
             dh1 = dqkv @ wf
             # LN1 backward (no dropout, no residual inside LN1: z = x); d z2 (the first residual's direct path) joins here
             dx, _, dg1, dbe1, _ = _ln_bwd_raw(dh1, x2d, mean1, rstd1, g1, 0.0, 0, dadd=dz2)
@@ -944,3 +951,36 @@ def vit_pre_ln_layer(x, heads, p_attn, p_hidden, ln1, q_lin, k_lin, v_lin, o_lin
     return _VitPreLNLayer.apply(x.contiguous(), cfg, q_lin.weight, k_lin.weight, v_lin.weight, q_lin.bias, k_lin.bias, v_lin.bias,
                                 wf, bf, o_lin.weight, o_lin.bias, ln1.weight, ln1.bias, fc1.weight, fc1.bias, fc2.weight,
                                 fc2.bias, ln2.weight, ln2.bias)
+
+
+class _ReplaceRows(torch.autograd.Function):
+    """``x[rows] = src`` IN PLACE (``x`` is returned, marked dirty).  ``x.index_copy(0, rows, src)`` copies all of ``x`` -- 367 MB
+    of packed text per fusion layer to rewrite 16 K bottleneck rows -- and its backward clones the whole gradient to zero
+    those rows.  Legal here because nothing saves ``x`` for its backward before the rows are rewritten (the LayerNorm kernels
+    save their pre-norm input, not their output); the backward zeroes the rows of the incoming gradient in place when that
+    gradient is a whole, contiguous tensor (it is the fresh ``dx`` of the block above), and clones otherwise."""
+
+    @staticmethod
+    def forward(ctx, x, rows, src):
+        x.index_copy_(0, rows, src)
+        ctx.mark_dirty(x)
+        ctx.save_for_backward(rows)
+        return x
+
+    @staticmethod
+    def backward(ctx, g):
+        (rows,) = ctx.saved_tensors
+        g_src = g.index_select(0, rows) if ctx.needs_input_grad[2] else None
+        g_x = None
+        if ctx.needs_input_grad[0]:
+            g_x = g if (g._base is None and g.is_contiguous()) else g.clone()
+            g_x.index_fill_(0, rows, 0)
+        return g_x, None, g_src
+
+
+def replace_rows(x: torch.Tensor, rows: torch.Tensor, src: torch.Tensor) -> torch.Tensor:
+    """``x.index_copy(0, rows, src)`` without copying ``x`` (see ``_ReplaceRows``); falls back to the out-of-place form for a
+    leaf that requires grad (autograd forbids in-place edits of those)."""
+    if x.is_leaf and x.requires_grad:
+        return x.index_copy(0, rows, src)
+    return _ReplaceRows.apply(x, rows, src)

@@ -209,3 +209,37 @@ def test_varlen_large_batch_matches_reference(ops):
         a, b = cul[s], cul[s + 1]
         ref = reference(qkv[a:b], [b - a], 64 ** -0.5)
         assert float((o[a:b].float() - ref).abs().max()) <= FWD_ATOL, s
+
+
+def _greedy_plan(lens, group):
+    """Python restatement of the grouping: consecutive sequences share an item while they fit 128 rows."""
+    items, rows, start, first, pos = [], [], 0, 0, 0
+    for s, n in enumerate(lens):
+        if s > first and (not group or pos + n - start > 128):
+            items.append((start, first))
+            start, first = pos, s
+        rows += [(pos - start, pos - start + n)] * n
+        pos += n
+    items.append((start, first))
+    return items, rows
+
+
+@pytest.mark.parametrize("n_seq,group", [(1, True), (7, True), (4096, True), (4096, False), (11264, True), (11300, True)])
+def test_varlen_plan_matches_greedy_restatement(ops, n_seq, group):
+    """The plan words (items, per-row key windows) bit for bit against the sequential greedy grouping: the pointer-doubling
+    kernels up to 11264 sequences, the single-thread kernel beyond."""
+    g = torch.Generator().manual_seed(n_seq)
+    lens = torch.randint(1, 129 if n_seq < 100 else 60, (n_seq,), generator=g).tolist()
+    lens[0] = 128
+    total = sum(lens)
+    cu = torch.tensor([0] + list(torch.tensor(lens).cumsum(0)), dtype=torch.int32).cuda()
+    plan = ops.varlen_plan(cu, total, group=group)
+    items, rows = _greedy_plan(lens, group)
+    assert not plan.error()
+    assert plan.n_items() == len(items)
+    w = plan.data.cpu().tolist()
+    got_items = [(w[4 + 2 * i], w[5 + 2 * i]) for i in range(len(items) + 1)]
+    assert got_items[:-1] == items and got_items[-1] == (total, n_seq)
+    off = 4 + 2 * (n_seq + 1) + n_seq
+    got_rows = [(x & 0xFFFF, x >> 16) for x in w[off:off + total]]
+    assert got_rows == rows

@@ -38,8 +38,10 @@ for n, v in step:
     a[0] += 1
     a[1] += v
 mine = ("mdt::", "attn_fwd_kernel", "attn_bwd_kernel", "apsp", "edges_to_adj", "node_feature", "move_rows", "attn_bias",
-        "attn_delta", "attn_dq", "mdt_", "attn::", "ln::")
+        "attn_delta", "attn_dq", "mdt_", "attn::", "ln::", "gelu::", "wgrad::", "gemm::", "varlen_plan")
 print(f"{'kernel':72s} {'count':>6s} {'total us':>11s} {'share':>7s} {'avg us':>9s}")
+lib = sum(t for k, (c, t) in agg.items() if "nvjet" in k or "cublas" in k or "cutlass" in k or "cudnn" in k)
+aten = sum(t for k, (c, t) in agg.items() if k.startswith("void at::") or "at_cuda_detail" in k or "elementwise_kernel_with_index" in k)
 for k, (c, t) in sorted(agg.items(), key=lambda kv: -kv[1][1])[:28]:
     print(f"{k:72s} {c:6d} {t:11.1f} {100 * t / tot:6.2f}% {t / c:9.1f}")
 print("\nkernels of libmdt_b200.so in this step:")
@@ -49,3 +51,5 @@ for k, (c, t) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
         print(f"{k:72s} {c:6d} {t:11.1f} {100 * t / tot:6.2f}% {t / c:9.1f}")
         mt += t
 print(f"libmdt_b200 total: {mt:.1f} us = {100 * mt / tot:.2f}% of the step")
+print(f"cuBLAS / cuDNN (nvjet_*, cutlass, cublasLt): {lib:.1f} us = {100 * lib / tot:.2f}%;  ATen element-wise / reduce / index / optimizer: "
+      f"{aten:.1f} us = {100 * aten / tot:.2f}%")
