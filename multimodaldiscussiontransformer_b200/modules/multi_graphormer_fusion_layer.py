@@ -121,7 +121,7 @@ def _varlen_attention(qkv, pack, dropout_p: float):
     return _FLASH(qkv, pack.cu_seqlens, pack.max_seqlen, dropout_p=dropout_p)
 
 
-def packed_bert_layer(layer, x: torch.Tensor, pack) -> torch.Tensor:
+def packed_bert_layer(layer, x: torch.Tensor, pack, take_rows=None):
     """Hugging Face ``BertLayer`` arithmetic (post-LN block, same parameters, same dropout rates) on packed tokens.
 
     The three projections run as ONE GEMM over the fused storage of the ``query / key / value`` parameters
@@ -140,7 +140,7 @@ def packed_bert_layer(layer, x: torch.Tensor, pack) -> torch.Tensor:
             raise RuntimeError(f"packed text attention handles sequences of <= 128 rows, got {pack.max_seqlen}")
         return ops.packed_post_ln_layer(x, pack.plan, H, sa.dropout.p, att.output.dropout.p, sa.query, sa.key, sa.value,
                                         att.output.dense, att.output.LayerNorm, layer.intermediate.dense, layer.output.dense,
-                                        layer.output.LayerNorm, layer.training)
+                                        layer.output.LayerNorm, layer.training, take_rows=take_rows)
     qkv = ops.linear_qkv(x, sa.query, sa.key, sa.value).view(-1, 3, H, d)
     ctx = _varlen_attention(qkv, pack, sa.dropout.p if layer.training else 0.0).reshape(x.shape)
     if x.dtype == torch.bfloat16 and x.shape[-1] in (256, 512, 768, 1024):
@@ -327,13 +327,18 @@ class GraphFusionLayer(nn.Module):
         (re)written from ``bottle_neck`` and read back after the BERT layer."""
         nb = self.num_bottle_neck_tokens
         C = x_packed.shape[-1]
-        x_packed = packed_bert_layer(self.bert_encoder, ops.replace_rows(x_packed, pack.bn_rows, bottle_neck.reshape(-1, C)), pack)
-        bottle_neck_output = x_packed.index_select(0, pack.bn_rows).view(-1, nb, C)
+        out = packed_bert_layer(self.bert_encoder, ops.replace_rows(x_packed, pack.bn_rows, bottle_neck.reshape(-1, C)), pack,
+                                take_rows=pack.bn_rows)
+        if isinstance(out, tuple):      # the single-node block hands the bottleneck rows out itself
+            x_packed, bn_rows_out = out
+        else:
+            x_packed, bn_rows_out = out, out.index_select(0, pack.bn_rows)
+        bottle_neck_output = bn_rows_out.view(-1, nb, C)
         if vit_hidden_states is not None:
             rows = image_rows(x_image_indexes)
             vit_out = self.vit_forward(prepend_tokens(bottle_neck.index_select(0, rows), vit_hidden_states))
-            vit_hidden_output = vit_out[:, nb:]
-            mixed = (vit_out[:, :nb] + bottle_neck_output.index_select(0, rows)) / 2
+            vit_bn, vit_hidden_output = ops.split_tokens(vit_out, nb) if vit_out.is_cuda else (vit_out[:, :nb], vit_out[:, nb:])
+            mixed = (vit_bn + bottle_neck_output.index_select(0, rows)) / 2
             bottle_neck_output = bottle_neck_output.index_copy(0, rows, mixed)
         else:
             vit_hidden_output = None

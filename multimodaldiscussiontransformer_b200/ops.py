@@ -739,7 +739,7 @@ class _PackedPostLNLayer(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, plan, cfg, wq, wk, wv, bq, bk, bv, wf, bf, wo, bo, g1, be1, w1, b1, w2, b2, g2, be2):
-        H, p_attn, p_hid, eps1, eps2, seeds = cfg
+        H, p_attn, p_hid, eps1, eps2, seeds, take = cfg
         lib = _lib.load()
         lin = torch.nn.functional.linear
         M, C = x.shape
@@ -754,18 +754,26 @@ class _PackedPostLNLayer(torch.autograd.Function):
             y, z2, mean2, rstd2 = _ln_fwd_raw(lin(g, w2, b2), h, g2, be2, p_hid, seeds[2], eps2)
         ctx.save_for_backward(x, qkv, att, lse, z1, mean1, rstd1, h, u, g, z2, mean2, rstd2, wf, wo, g1, w1, w2, g2)
         ctx.plan, ctx.cfg = plan, cfg
+        if take is not None:     # rows of y handed out as a second output: their gradient comes back as a second argument
+            return y, y.index_select(0, take)
         return y
 
     @staticmethod
-    def backward(ctx, dy):
+    def backward(ctx, dy, dtaken=None):
         x, qkv, att, lse, z1, mean1, rstd1, h, u, g, z2, mean2, rstd2, wf, wo, g1, w1, w2, g2 = ctx.saved_tensors
-        H, p_attn, p_hid, eps1, eps2, seeds = ctx.cfg
+        H, p_attn, p_hid, eps1, eps2, seeds, take = ctx.cfg
         lib = _lib.load()
         M, C = x.shape
         need = ctx.needs_input_grad   # 0 x | 3-5 wq wk wv | 6-8 bq bk bv | 11 wo 12 bo 13 g1 14 be1 15 w1 16 b1 17 w2 18 b2 19 g2 20 be2
         bdt = g1.dtype
         with torch.cuda.device(x.device):
             dy = dy.contiguous()
+            if dtaken is not None:
+                # the handed-out rows' gradient joins dy in place (16 K rows) instead of autograd's zero-filled [total, C]
+                # tensor + index_add + accumulation add; dy is the fresh dx of the block above unless it is a view
+                if dy._base is not None:
+                    dy = dy.clone()
+                dy.index_add_(0, take, dtaken.to(dy.dtype))
             # ---- feed-forward half (df may alias dh when there is no dropout: df is not read after dh is updated)
             df, dh, dg2, dbe2, db2 = _ln_bwd_raw(dy, z2, mean2, rstd2, g2, p_hid, seeds[2])
             dw2 = df.t() @ g if need[17] else None
@@ -794,15 +802,17 @@ class _PackedPostLNLayer(torch.autograd.Function):
                 db2.to(bdt), dg2.to(bdt), dbe2.to(bdt))
 
 
-def packed_post_ln_layer(x, plan, heads, p_attn, p_hidden, q_lin, k_lin, v_lin, o_lin, ln1, fc1, fc2, ln2, training):
+def packed_post_ln_layer(x, plan, heads, p_attn, p_hidden, q_lin, k_lin, v_lin, o_lin, ln1, fc1, fc2, ln2, training,
+                         take_rows=None):
     """One Hugging Face ``BertLayer`` (post-LN block) on packed rows ``x`` bf16 ``[total, C]`` (``C = 64 * heads`` in
-    {256, 512, 768, 1024}) as a single autograd node; the modules only lend their parameters."""
+    {256, 512, 768, 1024}) as a single autograd node; the modules only lend their parameters.  With ``take_rows`` (int64 row
+    list) returns ``(y, y[take_rows])``: the rows' gradient re-enters the node directly."""
     if not (x.is_cuda and x.dtype == torch.bfloat16 and x.dim() == 2 and x.shape[1] == 64 * heads):
         raise RuntimeError("ops.packed_post_ln_layer: bf16 CUDA rows [total, 64 * heads] (no other path)")
     wf, bf = fused_qkv_storage(q_lin, k_lin, v_lin)
     pa, ph = (float(p_attn), float(p_hidden)) if training else (0.0, 0.0)
     seeds = (next_seed() if pa > 0 else 0, next_seed() if ph > 0 else 0, next_seed() if ph > 0 else 0)
-    cfg = (int(heads), pa, ph, float(ln1.eps), float(ln2.eps), seeds)
+    cfg = (int(heads), pa, ph, float(ln1.eps), float(ln2.eps), seeds, take_rows)
     return _PackedPostLNLayer.apply(x.contiguous(), plan, cfg, q_lin.weight, k_lin.weight, v_lin.weight, q_lin.bias, k_lin.bias,
                                     v_lin.bias, wf, bf, o_lin.weight, o_lin.bias, ln1.weight, ln1.bias, fc1.weight, fc1.bias,
                                     fc2.weight, fc2.bias, ln2.weight, ln2.bias)
@@ -984,3 +994,33 @@ def replace_rows(x: torch.Tensor, rows: torch.Tensor, src: torch.Tensor) -> torc
     if x.is_leaf and x.requires_grad:
         return x.index_copy(0, rows, src)
     return _ReplaceRows.apply(x, rows, src)
+
+
+class _SplitTokens(torch.autograd.Function):
+    """``(x[:, :nb], x[:, nb:])``: autograd turns each slice's gradient into a zero-filled tensor of ``x``'s size and adds the two
+    (five passes over ``x``); the two gradients are disjoint, so the backward is one buffer and two copies."""
+
+    @staticmethod
+    def forward(ctx, x, nb):
+        ctx.nb, ctx.shape = nb, x.shape
+        return x[:, :nb], x[:, nb:]
+
+    @staticmethod
+    def backward(ctx, g0, g1):
+        B, T, C = ctx.shape
+        ref = g0 if g0 is not None else g1
+        out = torch.empty((B, T, C), dtype=ref.dtype, device=ref.device)
+        if g0 is not None:
+            out[:, :ctx.nb].copy_(g0)
+        else:
+            out[:, :ctx.nb].zero_()
+        if g1 is not None:
+            out[:, ctx.nb:].copy_(g1)
+        else:
+            out[:, ctx.nb:].zero_()
+        return out, None
+
+
+def split_tokens(x: torch.Tensor, nb: int):
+    """``x[:, :nb], x[:, nb:]`` of ``[B, T, C]`` with a single-buffer backward."""
+    return _SplitTokens.apply(x, nb)
