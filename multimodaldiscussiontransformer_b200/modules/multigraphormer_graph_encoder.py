@@ -17,7 +17,7 @@ from .. import ops
 from ._fairseq_compat import FairseqDropout, LayerNorm
 from .graphormer_graph_encoder_layer import GraphEncoderStack
 from .graphormer_layers import GraphAttnBias, GraphNodeFeature
-from .multi_graphormer_fusion_layer import (GraphFusionStack, TextPack, image_rows, packed_bert_layer, use_fused_intermediates, use_fused_vit_layers,
+from .multi_graphormer_fusion_layer import (GraphFusionStack, TextPack, image_rows, packed_bert_layer, use_fused_intermediates, use_fused_vit_layers, use_patch_gemm,
                                             use_fused_layer_norms, use_mdt_attention)
 from .multihead_attention import MultiheadAttention
 
@@ -98,6 +98,8 @@ class MultiGraphormerGraphEncoder(nn.Module):
         use_mdt_attention(self.vit_model)      # ... and their self-attention on the tcgen05 kernels
         use_fused_intermediates(self.vit_model)  # ... and dense -> GELU on csrc/gelu.cu
         use_fused_vit_layers(self.vit_model)     # ... and each block as one node (residual adds / dropouts fused)
+        use_patch_gemm(self.vit_model)           # ... and the patch embedding as the GEMM it is
+        use_fused_layer_norms(self.text_model)   # the BERT embeddings' LayerNorm (the blocks' LayerNorms are fused with their tails)
         use_fused_intermediates(self.text_model)
         self.fusion_layers = nn.ModuleList([
             GraphFusionStack(t, v, num_bottle_neck, use_projection=True)

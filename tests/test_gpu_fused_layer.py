@@ -247,3 +247,21 @@ def test_fusion_layer_routes_vit_through_the_single_node():
     fl.vit_forward(x).sum().backward()
     assert _lib.CALLS.get("mdt_dropout_bwd", 0) == before + 1
     assert x.grad is not None and bool(torch.isfinite(x.grad).all())
+
+
+def test_patch_embedding_as_gemm_matches_the_convolution():
+    from transformers import ViTConfig
+    from transformers.models.vit.modeling_vit import ViTPatchEmbeddings
+
+    from multimodaldiscussiontransformer_b200.modules.multi_graphormer_fusion_layer import use_patch_gemm
+
+    torch.manual_seed(0)
+    pe = ViTPatchEmbeddings(ViTConfig()).cuda().bfloat16()
+    x = torch.randn(5, 3, 224, 224, device="cuda").bfloat16()
+    want = pe(x).float()
+    keys = list(pe.state_dict().keys())
+    got = use_patch_gemm(pe)(x).float()
+    assert list(pe.state_dict().keys()) == keys and got.shape == want.shape == (5, 196, 768)
+    assert float((got - want).abs().max()) <= 2e-2 * max(1.0, float(want.abs().max()))
+    want32 = torch.nn.functional.conv2d(x.float(), pe.projection.weight.float(), pe.projection.bias.float(), stride=16)
+    assert float((got - want32.flatten(2).transpose(1, 2)).abs().max()) <= 2e-2 * max(1.0, float(want32.abs().max()))
