@@ -19,6 +19,18 @@ def _first(out):
     return out[0] if isinstance(out, (tuple, list)) else out
 
 
+def _rows_i32(rows: torch.Tensor) -> torch.Tensor:
+    """int32 copy of a row list, cached on the tensor (one conversion per batch, not per layer)."""
+    r = getattr(rows, "_mdt_i32", None)
+    if r is None:
+        r = rows.to(torch.int32).contiguous()
+        try:
+            rows._mdt_i32 = r
+        except Exception:
+            pass
+    return r
+
+
 def image_rows(x_image_indexes: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
     """bool ``[n_real]`` (reference format; costs one device->host sync) or int row list -> int64 rows."""
     if x_image_indexes is None:
@@ -257,7 +269,7 @@ class FusedViTLayer(nn.Module):
     """Hugging Face ``ViTLayer`` (same parameters and state-dict keys) whose bf16 CUDA forward is the single autograd node
     ``ops.vit_pre_ln_layer``; anything else (fp32 parity runs, ``MDT_FUSED_VIT_LAYER=0``) takes Hugging Face's forward."""
 
-    def forward(self, hidden_states, *args, **kwargs):
+    def forward(self, hidden_states, *args, take_tokens=None, **kwargs):
         sa = self.attention.attention
         if (FUSED_VIT_LAYER and VIT_ATTN_IMPL == "mdt" and hidden_states.is_cuda and hidden_states.dtype == torch.bfloat16
                 and hidden_states.dim() == 3 and hidden_states.shape[-1] in (256, 512, 768, 1024)
@@ -265,7 +277,8 @@ class FusedViTLayer(nn.Module):
                 and getattr(self.intermediate, "_mdt_exact_gelu", False) and not args and not kwargs):
             return ops.vit_pre_ln_layer(hidden_states, sa.num_attention_heads, sa.dropout_prob, self.output.dropout.p,
                                         self.layernorm_before, sa.query, sa.key, sa.value, self.attention.output.dense,
-                                        self.layernorm_after, self.intermediate.dense, self.output.dense, self.training)
+                                        self.layernorm_after, self.intermediate.dense, self.output.dense, self.training,
+                                        take_tokens=take_tokens)
         return super().forward(hidden_states, *args, **kwargs)
 
 
@@ -364,10 +377,31 @@ class GraphFusionLayer(nn.Module):
         bottle_neck_output = bn_rows_out.view(-1, nb, C)
         if vit_hidden_states is not None:
             rows = image_rows(x_image_indexes)
-            vit_out = self.vit_forward(prepend_tokens(bottle_neck.index_select(0, rows), vit_hidden_states))
-            vit_bn, vit_hidden_output = ops.split_tokens(vit_out, nb) if vit_out.is_cuda else (vit_out[:, :nb], vit_out[:, nb:])
-            mixed = (vit_bn + bottle_neck_output.index_select(0, rows)) / 2
-            bottle_neck_output = bottle_neck_output.index_copy(0, rows, mixed)
+            if isinstance(self.vit_encoder, FusedViTLayer) and x_packed.is_cuda:
+                # The ViT tokens live in ONE [n_img, nb + 197, C] buffer across the fusion layers: its bottleneck slots are
+                # rewritten in place, the block hands its first nb output tokens out itself, row moves go through
+                # mdt_gather_rows / mdt_scatter_rows (ATen's index_add for 380 rows of 3072 elements takes 92 us).
+                rows32 = _rows_i32(rows)
+                n = bottle_neck.shape[0]
+                bn_img = ops.gather_rows(bottle_neck.reshape(n, nb * C), rows32).view(-1, nb, C)
+                if getattr(vit_hidden_states, "_mdt_has_bn", False):
+                    x_vit = ops.replace_tokens(vit_hidden_states, bn_img)
+                else:
+                    x_vit = prepend_tokens(bn_img, vit_hidden_states)
+                out = self.vit_encoder(x_vit, take_tokens=nb)
+                if isinstance(out, tuple):
+                    vit_hidden_output, vit_bn = out
+                    vit_hidden_output._mdt_has_bn = True
+                else:
+                    vit_bn, vit_hidden_output = ops.split_tokens(_first(out), nb)
+                bno = bottle_neck_output.reshape(n, nb * C)
+                mixed = (vit_bn.reshape(-1, nb * C) + ops.gather_rows(bno, rows32)) / 2
+                bottle_neck_output = ops.scatter_rows(bno, mixed, rows32).view(n, nb, C)
+            else:
+                vit_out = self.vit_forward(prepend_tokens(bottle_neck.index_select(0, rows), vit_hidden_states))
+                vit_bn, vit_hidden_output = vit_out[:, :nb], vit_out[:, nb:]
+                mixed = (vit_bn + bottle_neck_output.index_select(0, rows)) / 2
+                bottle_neck_output = bottle_neck_output.index_copy(0, rows, mixed)
         else:
             vit_hidden_output = None
         return x_packed, vit_hidden_output, bottle_neck_output

@@ -854,9 +854,9 @@ class _Ctx:
         self.saved_tensors = t
 
 
-def _dropout_add_raw(x2, r2, p, seed):
+def _dropout_add_raw(x2, r2, p, seed, out_shape=None):
     lib = _lib.load()
-    y = torch.empty_like(x2)
+    y = torch.empty_like(x2) if out_shape is None else torch.empty(out_shape, dtype=x2.dtype, device=x2.device)
     _lib.check(lib.mdt_dropout_add_fwd(_lib.ptr(x2), _lib.ptr(r2), _lib.ptr(y), x2.shape[0], x2.shape[1], float(p), int(seed),
                                        _lib.stream()), "mdt_dropout_add_fwd")
     return y
@@ -875,7 +875,7 @@ def _dropout_bwd_raw(dy2, p, seed, want_dx=True):
 class _VitPreLNLayer(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, cfg, wq, wk, wv, bq, bk, bv, wf, bf, wo, bo, g1, be1, w1, b1, w2, b2, g2, be2):
-        H, p_attn, p_hid, eps1, eps2, seeds = cfg
+        H, p_attn, p_hid, eps1, eps2, seeds, take = cfg
         lib = _lib.load()
         lin = torch.nn.functional.linear
         Bn, T, C = x.shape
@@ -896,20 +896,27 @@ class _VitPreLNLayer(torch.autograd.Function):
             u = lin(h2, w1, b1)
             g = torch.empty_like(u)
             _lib.check(lib.mdt_gelu_fwd(_lib.ptr(u), _lib.ptr(g), u.shape[0], u.shape[1], _lib.stream()), "mdt_gelu_fwd")
-            y = _dropout_add_raw(lin(g, w2, b2), z2, p_hid, seeds[2])
+            y = _dropout_add_raw(lin(g, w2, b2), z2, p_hid, seeds[2], out_shape=(Bn, T, C))   # a base tensor, not a view:
+            #                                                  the next layer rewrites its bottleneck slots in place
         ctx.save_for_backward(x2d, h1, mean1, rstd1, att2, z2, mean2, rstd2, h2, u, g, ws, wo, g1, w1, w2, g2, *actx.saved_tensors[:5])
         ctx.cfg, ctx.shape = cfg, (Bn, T, C)
-        return y.view(Bn, T, C)
+        if take is not None:      # the first `take` tokens handed out as a second output (see _PackedPostLNLayer)
+            return y, y[:, :take].clone()
+        return y
 
     @staticmethod
-    def backward(ctx, dy):
+    def backward(ctx, dy, dtaken=None):
         (x2d, h1, mean1, rstd1, att2, z2, mean2, rstd2, h2, u, g, wf, wo, g1, w1, w2, g2, q, k, v, aout, lse) = ctx.saved_tensors
-        H, p_attn, p_hid, eps1, eps2, seeds = ctx.cfg
+        H, p_attn, p_hid, eps1, eps2, seeds, take = ctx.cfg
         Bn, T, C = ctx.shape
         lib = _lib.load()
         need = ctx.needs_input_grad   # 0 x | 2-4 wq wk wv | 5-7 bq bk bv | 10 wo 11 bo 12 g1 13 be1 14 w1 15 b1 16 w2 17 b2 18 g2 19 be2
         bdt = g1.dtype
         with torch.cuda.device(dy.device):
+            if dtaken is not None:    # joins dy in place when dy is a whole tensor (the fresh dx of the block above)
+                if dy._base is not None or not dy.is_contiguous():
+                    dy = dy.contiguous().clone() if dy.is_contiguous() else dy.contiguous()
+                dy[:, :take].add_(dtaken)
             dy2 = dy.reshape(Bn * T, C).contiguous()
             # ---- feed-forward half: y = drop(f) + z2
             df, db2 = _dropout_bwd_raw(dy2, p_hid, seeds[2])
@@ -949,15 +956,16 @@ class _VitPreLNLayer(torch.autograd.Function):
                 db1.to(bdt), dw2, db2.to(bdt), dg2.to(bdt), dbe2.to(bdt))
 
 
-def vit_pre_ln_layer(x, heads, p_attn, p_hidden, ln1, q_lin, k_lin, v_lin, o_lin, ln2, fc1, fc2, training):
+def vit_pre_ln_layer(x, heads, p_attn, p_hidden, ln1, q_lin, k_lin, v_lin, o_lin, ln2, fc1, fc2, training, take_tokens=None):
     """One Hugging Face ``ViTLayer`` (pre-LN block) on ``x`` bf16 ``[B, T, C]`` (``C = 64 * heads`` in {256, 512, 768, 1024})
-    as a single autograd node; the modules only lend their parameters."""
+    as a single autograd node; the modules only lend their parameters.  With ``take_tokens = nb`` returns
+    ``(y, y[:, :nb] copy)``: the copy's gradient re-enters the node directly."""
     if not (x.is_cuda and x.dtype == torch.bfloat16 and x.dim() == 3 and x.shape[2] == 64 * heads):
         raise RuntimeError("ops.vit_pre_ln_layer: bf16 CUDA [B, T, 64 * heads] (no other path)")
     wf, bf = fused_qkv_storage(q_lin, k_lin, v_lin)
     pa, ph = (float(p_attn), float(p_hidden)) if training else (0.0, 0.0)
     seeds = (next_seed() if pa > 0 else 0, next_seed() if ph > 0 else 0, next_seed() if ph > 0 else 0)
-    cfg = (int(heads), pa, ph, float(ln1.eps), float(ln2.eps), seeds)
+    cfg = (int(heads), pa, ph, float(ln1.eps), float(ln2.eps), seeds, take_tokens)
     return _VitPreLNLayer.apply(x.contiguous(), cfg, q_lin.weight, k_lin.weight, v_lin.weight, q_lin.bias, k_lin.bias, v_lin.bias,
                                 wf, bf, o_lin.weight, o_lin.bias, ln1.weight, ln1.bias, fc1.weight, fc1.bias, fc2.weight,
                                 fc2.bias, ln2.weight, ln2.bias)
@@ -1024,3 +1032,31 @@ class _SplitTokens(torch.autograd.Function):
 def split_tokens(x: torch.Tensor, nb: int):
     """``x[:, :nb], x[:, nb:]`` of ``[B, T, C]`` with a single-buffer backward."""
     return _SplitTokens.apply(x, nb)
+
+
+class _ReplaceTokens(torch.autograd.Function):
+    """``x[:, :nb] = src`` IN PLACE on ``[B, T, C]`` (the bottleneck slots of the ViT buffer; see ``_ReplaceRows``)."""
+
+    @staticmethod
+    def forward(ctx, x, src):
+        nb = src.shape[1]
+        x[:, :nb].copy_(src)
+        ctx.mark_dirty(x)
+        ctx.nb = nb
+        return x
+
+    @staticmethod
+    def backward(ctx, g):
+        nb = ctx.nb
+        g_src = g[:, :nb].clone() if ctx.needs_input_grad[1] else None
+        g_x = None
+        if ctx.needs_input_grad[0]:
+            g_x = g if (g._base is None and g.is_contiguous()) else g.clone()
+            g_x[:, :nb].zero_()
+        return g_x, g_src
+
+
+def replace_tokens(x: torch.Tensor, src: torch.Tensor) -> torch.Tensor:
+    if x.is_leaf and x.requires_grad:
+        return torch.cat([src, x[:, src.shape[1]:]], dim=1)
+    return _ReplaceTokens.apply(x, src)
