@@ -298,9 +298,11 @@ int mdt_gemm_bias_act(const void *a, int64_t lda, const void *w, int64_t ldw, co
 /* N2  weight gradient of a dense layer: out[N, C] += dy[M, N]^T * x[M, C]   (torch: dy.t() @ x; Hugging Face dense layers called
  *     from mDT/src/modules/multi_graphormer_fusion_layer.py:94-98,138-148, backward pass)
  *   dy, x bf16 row-major with leading dimensions ldy, ldx (elements, multiples of 8); out fp32 [N, ldo], ACCUMULATED into with
- *   vector atomics (split-K: the caller zeroes it, or passes a running fp32 gradient); N, C multiples of 256; M < 2^31 rows. */
-int mdt_wgrad_gemm(const void *dy, int64_t ldy, const void *x, int64_t ldx, float *out, int64_t ldo, int64_t M, int N, int C,
-                   mdt_stream_t stream);
+ *   vector atomics (split-K: the caller zeroes it, or passes a running fp32 gradient); N, C multiples of 256; M < 2^31 rows.
+ *   colsum fp32 [N] (may be NULL) += the column sums of dy -- the bias gradient of the same layer -- added up from the tiles
+ *   the kernel has staged anyway. */
+int mdt_wgrad_gemm(const void *dy, int64_t ldy, const void *x, int64_t ldx, float *out, int64_t ldo, float *colsum, int64_t M,
+                   int N, int C, mdt_stream_t stream);
 
 /* Self-test of the tcgen05 building blocks (shared-memory descriptor layouts, TMA 128-byte
  * swizzle, TMEM read-back); called by tests/ only.  All operands bf16, row major:

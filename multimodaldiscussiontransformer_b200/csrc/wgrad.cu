@@ -11,7 +11,9 @@
 //   warp 1     MMA issuer: per block 4 k-steps x 2 tcgen05.mma 128 x 256 x 16 (A = dY columns as M, B = X columns as N, both
 //              MN-major) into two 256-column TMEM accumulators (all 512 columns)
 //   warps 2-9  epilogue, once per CTA: TMEM -> registers -> red.global.add.v4.f32 into the fp32 output (the caller zeroes it;
-//              the splits of a tile meet there)
+//              the splits of a tile meet there).  While the main loop runs, two of them (in the CTAs of the first column tile)
+//              optionally add up the dY columns from the staged tiles: colsum[n] += sum_m dY[m][n], the bias gradient of the
+//              same dense layer, without another pass over dY
 // Rows past M are zero-filled by TMA and add nothing.
 #include "umma.cuh"
 
@@ -37,6 +39,7 @@ struct Args {
     int splits, kb_per_split;
     float *out;         // [N, ldo] fp32, accumulated into
     int64_t ldo;
+    float *colsum;      // [N] fp32 or null: += column sums of dy
 };
 
 __global__ void __launch_bounds__(kThreads, 1)
@@ -52,11 +55,12 @@ __global__ void __launch_bounds__(kThreads, 1)
     const int kb1 = min(n_kb_all, kb0 + a.kb_per_split);
     const int n_kb = max(kb1 - kb0, 0);
 
+    const bool do_colsum = a.colsum != nullptr && c0 == 0;   // CTA-uniform
     if (tid == 0) {
         if (smem_u32(smem) & 1023u) __trap();
         for (int s = 0; s < kStages; ++s) {
             mbar_init(&ctl.full[s], 1);
-            mbar_init(&ctl.empty[s], 1);
+            mbar_init(&ctl.empty[s], do_colsum ? 3 : 1);   // the MMA commit (+ the two column-sum warps)
         }
         mbar_init(&ctl.acc_full, 1);
         fence_barrier_init();
@@ -109,6 +113,28 @@ __global__ void __launch_bounds__(kThreads, 1)
                 umma_commit(&ctl.acc_full);
             }
         } else {
+            if (do_colsum && warp < 4) {
+                // warps 2, 3: thread t owns dY columns [4 t, 4 t + 4) of the tile; 64 rows per stage as 8-byte reads
+                const int t = tid - 64;
+                const uint32_t atom = (uint32_t)(t >> 4) * kAtom, c16 = (uint32_t)(t & 15) >> 1, sub = (uint32_t)(t & 1) * 8;
+                float acc[4] = {0.f, 0.f, 0.f, 0.f};
+                for (int g = 0; g < n_kb; ++g) {
+                    const int s = g % kStages;
+                    mbar_wait(&ctl.full[s], (g / kStages) & 1);
+                    const uint32_t base = smem_u32(smem + s * kStageBytes) + atom + sub;
+#pragma unroll 8
+                    for (int r = 0; r < kBK; ++r) {
+                        uint32_t w0, w1;
+                        asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(w0), "=r"(w1) : "r"(base + r * 128 + ((c16 ^ (r & 7)) << 4)));
+                        acc[0] += __uint_as_float(w0 << 16), acc[1] += __uint_as_float(w0 & 0xffff0000u);
+                        acc[2] += __uint_as_float(w1 << 16), acc[3] += __uint_as_float(w1 & 0xffff0000u);
+                    }
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&ctl.empty[s]);
+                }
+#pragma unroll
+                for (int i = 0; i < 4; ++i) atomicAdd(a.colsum + n0 + 4 * t + i, acc[i]);
+            }
             const int q = warp & 3;              // TMEM lane quarter this warp may read
             const int h = (warp - 2) >> 2;       // accumulator (128-row half of the tile)
             const int n = n0 + h * 128 + q * 32 + lane;
@@ -139,9 +165,10 @@ __global__ void __launch_bounds__(kThreads, 1)
 using namespace mdt;
 
 // out[N, C] (fp32, leading dimension ldo, ACCUMULATED into: the caller zeroes it) += dy[M, N]^T * x[M, C]; dy, x bf16 row-major
-// with leading dimensions ldy, ldx (elements, multiples of 8).  N and C multiples of 256.
-extern "C" int mdt_wgrad_gemm(const void *dy, int64_t ldy, const void *x, int64_t ldx, float *out, int64_t ldo, int64_t M, int N,
-                              int C, mdt_stream_t stream) {
+// with leading dimensions ldy, ldx (elements, multiples of 8).  N and C multiples of 256.  colsum (fp32 [N], may be null) +=
+// the column sums of dy.
+extern "C" int mdt_wgrad_gemm(const void *dy, int64_t ldy, const void *x, int64_t ldx, float *out, int64_t ldo, float *colsum,
+                              int64_t M, int N, int C, mdt_stream_t stream) {
     if (int rc = require_sm100()) return rc;
     MDT_REQUIRE(dy && x && out && M >= 1 && M < (int64_t)1 << 31, "mdt_wgrad_gemm: dy, x, out must be non-null and 1 <= M < 2^31");
     MDT_REQUIRE(N >= wgrad::kT && C >= wgrad::kT && N % wgrad::kT == 0 && C % wgrad::kT == 0,
@@ -160,7 +187,7 @@ extern "C" int mdt_wgrad_gemm(const void *dy, int64_t ldy, const void *x, int64_
         if (int rc = make_tensor_map_bf16(&mx, x, 2, dims, str, box)) return rc;
     }
     wgrad::Args g{};
-    g.M = (int)M, g.N = N, g.C = C, g.out = out, g.ldo = ldo;
+    g.M = (int)M, g.N = N, g.C = C, g.out = out, g.ldo = ldo, g.colsum = colsum;
     const int tiles = (N / wgrad::kT) * (C / wgrad::kT);
     const int n_kb = (int)((M + wgrad::kBK - 1) / wgrad::kBK);
     int splits = num_sms() / tiles;

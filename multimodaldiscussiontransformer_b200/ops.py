@@ -725,13 +725,17 @@ def _varlen_bwd_raw(qkv, out, lse, plan, go, p, seed, scale):
     return dqkv
 
 
-def _wgrad(dy2, x2):
+def _wgrad(dy2, x2, with_colsum=False):
     """``dy2.t() @ x2`` in the parameter dtype: this library's split-K kernel where it wins over cuBLAS (output columns <= 768,
-    both output dimensions multiples of 256; benchmarks/wgrad_microbench.py), cuBLAS otherwise."""
+    both output dimensions multiples of 256; benchmarks/wgrad_microbench.py), cuBLAS otherwise.  ``with_colsum``: returns
+    ``(dW, dy2.sum(0) in fp32)``, the sums coming out of the same pass on the own kernel."""
     N, C = dy2.shape[1], x2.shape[1]
     if OWN_WGRAD and N % 256 == 0 and C % 256 == 0 and C <= 768 and dy2.shape[0] >= 32768:
-        return wgrad_gemm(dy2, x2).to(dy2.dtype)
-    return dy2.t() @ x2
+        cs = torch.zeros(N, dtype=torch.float32, device=dy2.device) if with_colsum else None
+        dw = wgrad_gemm(dy2, x2, colsum=cs).to(dy2.dtype)
+        return (dw, cs) if with_colsum else dw
+    dw = dy2.t() @ x2
+    return (dw, dy2.sum(0, dtype=torch.float32)) if with_colsum else dw
 
 
 class _PackedPostLNLayer(torch.autograd.Function):
@@ -790,8 +794,8 @@ class _PackedPostLNLayer(torch.autograd.Function):
             datt = da @ wo
             dqkv = _varlen_bwd_raw(qkv, att.view(M, H, 64), lse, ctx.plan, datt.view(M, H, 64), p_attn, seeds[0], 64 ** -0.5)
             dqkv = dqkv.view(M, 3 * C)
-            dwf = _wgrad(dqkv, x) if any(need[3:6]) else None
-            dbf = dqkv.sum(0) if any(need[6:9]) else None
+            dwf, dbf = _wgrad(dqkv, x, with_colsum=True)
+            dbf = dbf.to(bdt)
             if need[0]:
                 dx.addmm_(dqkv, wf)
             else:
@@ -818,9 +822,10 @@ def packed_post_ln_layer(x, plan, heads, p_attn, p_hidden, q_lin, k_lin, v_lin, 
                                     fc2.weight, fc2.bias, ln2.weight, ln2.bias)
 
 
-def wgrad_gemm(dy: torch.Tensor, x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+def wgrad_gemm(dy: torch.Tensor, x: torch.Tensor, out: Optional[torch.Tensor] = None, colsum: Optional[torch.Tensor] = None) -> torch.Tensor:
     """``dy.t() @ x`` for bf16 ``dy [M, N]``, ``x [M, C]`` (N, C multiples of 256) on this library's split-K tcgen05 kernel
-    (csrc/wgrad.cu) -> fp32 ``[N, C]``; with ``out`` the product is accumulated into it."""
+    (csrc/wgrad.cu) -> fp32 ``[N, C]``; with ``out`` the product is accumulated into it; ``colsum`` (fp32 ``[N]``) receives
+    ``+= dy.sum(0)`` from the same pass."""
     lib = _lib.load()
     _require_cuda(dy, x)
     if dy.dtype != torch.bfloat16 or x.dtype != torch.bfloat16 or dy.dim() != 2 or x.dim() != 2 or dy.shape[0] != x.shape[0]:
@@ -834,8 +839,8 @@ def wgrad_gemm(dy: torch.Tensor, x: torch.Tensor, out: Optional[torch.Tensor] = 
     if out is None:
         out = torch.zeros((N, C), dtype=torch.float32, device=dy.device)
     with torch.cuda.device(dy.device):
-        _lib.check(lib.mdt_wgrad_gemm(_lib.ptr(dy), dy.stride(0), _lib.ptr(x), x.stride(0), _lib.ptr(out), out.stride(0), M, N, C,
-                                      _lib.stream()), "mdt_wgrad_gemm")
+        _lib.check(lib.mdt_wgrad_gemm(_lib.ptr(dy), dy.stride(0), _lib.ptr(x), x.stride(0), _lib.ptr(out), out.stride(0),
+                                      _lib.ptr(colsum), M, N, C, _lib.stream()), "mdt_wgrad_gemm")
     return out
 
 
@@ -941,12 +946,10 @@ class _VitPreLNLayer(torch.autograd.Function):
             actx.grad_views = (dqkv[:, :, 0], dqkv[:, :, 1], dqkv[:, :, 2])
             _BiasedAttention.backward(actx, datt)
             dqkv = dqkv.view(Bn * T, 3 * C)      # gradient w.r.t. [q / 8 | k | v]: wf here is the weight with its q rows / 8
-            dwf = _wgrad(dqkv, h1) if any(need[2:5]) else None
-            dbf = dqkv.sum(0) if any(need[5:8]) else None
-            if dwf is not None:
-                dwf[:C].mul_(0.125)
-            if dbf is not None:
-                dbf[:C].mul_(0.125)
+            dwf, dbf = _wgrad(dqkv, h1, with_colsum=True)
+            dbf = dbf.to(bdt)
+            dwf[:C].mul_(0.125)
+            dbf[:C].mul_(0.125)
             dh1 = dqkv @ wf
             # LN1 backward (no dropout, no residual inside LN1: z = x); d z2 (the first residual's direct path) joins here
             dx, _, dg1, dbe1, _ = _ln_bwd_raw(dh1, x2d, mean1, rstd1, g1, 0.0, 0, dadd=dz2)

@@ -194,5 +194,11 @@ def test_own_weight_gradient_gemm(M, N, C):
     acc = base.clone()
     ops.wgrad_gemm(dy, x, out=acc)
     assert float((acc.double() - base.double() - want).abs().max()) <= 2e-5 * scale + 1e-5
+    # the column sums of dy (bias gradient) from the same pass, accumulated
+    cs = torch.full((N,), 0.5, dtype=torch.float32, device="cuda")
+    got2 = ops.wgrad_gemm(dy, x, colsum=cs)
+    assert torch.equal(got2, got) or float((got2 - got).abs().max()) <= 2e-5 * scale      # atomics: order may differ
+    want_cs = dy.double().sum(0) + 0.5
+    assert float((cs.double() - want_cs).abs().max()) <= 1e-5 * max(1.0, float(want_cs.abs().max()))
     with pytest.raises(RuntimeError):
         ops.wgrad_gemm(dy[:, :200], x)                                 # N must be a multiple of 256
