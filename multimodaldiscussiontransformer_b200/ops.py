@@ -748,6 +748,9 @@ def _wgrad(dy2, x2, with_colsum=False):
         cs = torch.zeros(N, dtype=torch.float32, device=dy2.device) if with_colsum else None
         dw = wgrad_gemm(dy2, x2, colsum=cs).to(dy2.dtype)
         return (dw, cs) if with_colsum else dw
+    if (OWN_WGRAD and not with_colsum and N % 256 == 0 and C % 256 == 0 and N <= 768 and dy2.shape[0] >= 131072):
+        # wide outputs (fc2: 768 x 3072) as the transpose of the narrow product the kernel is good at (732 vs cuBLAS 822 us)
+        return wgrad_gemm(x2, dy2).t().contiguous().to(dy2.dtype)
     dw = dy2.t() @ x2
     return (dw, dy2.sum(0, dtype=torch.float32)) if with_colsum else dw
 
