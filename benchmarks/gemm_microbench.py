@@ -24,7 +24,8 @@ def timed(fn, iters=10):
 
 
 peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.isfile(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {"bf16_tflops": 1590.0}
-for M, N, K in ((238806, 3072, 768), (82410, 3072, 768), (4128, 768, 768), (1000, 256, 64)):
+for M, N, K in ((238806, 3072, 768), (238806, 2304, 768), (238806, 768, 768), (238806, 768, 3072), (82410, 3072, 768), (82410, 2304, 768),
+                (82410, 768, 768), (82410, 768, 3072), (4128, 768, 768), (1000, 256, 64)):
     g = torch.Generator(device="cuda").manual_seed(M)
     x = (torch.randn(M, K, device="cuda", generator=g)).bfloat16()
     w = (torch.randn(N, K, device="cuda", generator=g) * K ** -0.5).bfloat16()

@@ -20,7 +20,7 @@ PKG = os.path.dirname(HERE)
 ROOT = os.path.dirname(PKG)
 LIB = os.path.join(PKG, "libmdt_b200.so")
 OBJ_DIR = os.path.join(HERE, "_obj")
-SOURCES = ["runtime.cu", "tensor_map.cu", "apsp.cu", "attn_bias.cu", "rows.cu", "layernorm.cu", "gelu.cu", "gemm.cu", "wgrad.cu", "attn_fwd.cu", "attn_fwd3.cu", "attn_tail.cu", "attn_bwd.cu", "attn_bwd2.cu", "attn_varlen.cu", "umma_selftest.cu"]
+SOURCES = ["runtime.cu", "tensor_map.cu", "apsp.cu", "attn_bias.cu", "rows.cu", "layernorm.cu", "gelu.cu", "gemm.cu", "gemm2.cu", "wgrad.cu", "attn_fwd.cu", "attn_fwd3.cu", "attn_tail.cu", "attn_bwd.cu", "attn_bwd2.cu", "attn_varlen.cu", "umma_selftest.cu"]
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", "-Xptxas", "-v"]
 

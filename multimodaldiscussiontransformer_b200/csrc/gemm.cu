@@ -13,6 +13,8 @@
 // Epilogue modes: kEpiBias (out = acc + bias) and kEpiBiasGelu (aux = acc + bias, out = gelu(aux): the activation costs one
 // extra write of `out` instead of a separate read + write pass over [M, N]).
 // Shared memory 4 x 48 KB; TMEM 512 columns; rows past M are zero-filled by TMA on the way in and masked on the way out.
+#include <cstdlib>
+
 #include "umma.cuh"
 
 namespace mdt {
@@ -189,6 +191,9 @@ __global__ void __launch_bounds__(kThreads, 1)
 
 using namespace mdt;
 
+int mdt_gemm_pair_launch(const void *a, int64_t lda, const void *w, int64_t ldw, const void *bias, void *out, void *aux, int M, int N,
+                         int K, int act, cudaStream_t stream);   // gemm2.cu
+
 // out[M,N] = a[M,K] * w[N,K]^T + bias, optionally followed by the exact GELU (then aux receives the pre-activation).
 // bf16 row-major tensors with the given leading dimensions of a and w (elements); out / aux are dense [M,N].
 extern "C" int mdt_gemm_bias_act(const void *a, int64_t lda, const void *w, int64_t ldw, const void *bias, void *out, void *aux,
@@ -199,6 +204,9 @@ extern "C" int mdt_gemm_bias_act(const void *a, int64_t lda, const void *w, int6
     MDT_REQUIRE(act == 0 || (act == 1 && aux != nullptr), "mdt_gemm_bias_act: act is 0 (bias) or 1 (bias + GELU, needs aux)");
     MDT_REQUIRE(lda % 8 == 0 && ldw % 8 == 0 && lda >= K && ldw >= K, "mdt_gemm_bias_act: leading dimensions must be multiples of 8 and >= K");
     MDT_REQUIRE((((uintptr_t)out | (uintptr_t)aux | (uintptr_t)bias) & 15) == 0, "mdt_gemm_bias_act: out, aux, bias must be 16-byte aligned");
+    // CTA-pair kernel (gemm2.cu): MDT_GEMM_PAIR=0 keeps the single-CTA kernel below (A/B runs)
+    static const bool use_pair = []() { const char *e = getenv("MDT_GEMM_PAIR"); return !(e && e[0] == '0'); }();
+    if (use_pair) return mdt_gemm_pair_launch(a, lda, w, ldw, bias, out, aux, M, N, K, act, as_stream(stream));
     CUtensorMap ma, mw;
     {
         const uint64_t dims[2] = {(uint64_t)K, (uint64_t)M}, str[2] = {2, (uint64_t)lda * 2};

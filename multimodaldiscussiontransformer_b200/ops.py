@@ -561,10 +561,8 @@ class _LinearGelu(torch.autograd.Function):
     def forward(ctx, x, weight, bias):
         lib = _lib.load()
         x2 = x.reshape(-1, x.shape[-1])
-        u = torch.nn.functional.linear(x2, weight, bias)
-        g = torch.empty_like(u)
         with torch.cuda.device(x.device):
-            _lib.check(lib.mdt_gelu_fwd(_lib.ptr(u), _lib.ptr(g), u.shape[0], u.shape[1], _lib.stream()), "mdt_gelu_fwd")
+            g, u = _dense_gelu(x2, weight, bias)
         ctx.save_for_backward(x2, weight, u)
         ctx.has_bias = bias is not None
         ctx.bias_dtype = bias.dtype if bias is not None else None
@@ -755,6 +753,23 @@ def _wgrad(dy2, x2, with_colsum=False):
     return (dw, dy2.sum(0, dtype=torch.float32)) if with_colsum else dw
 
 
+#: MDT_OWN_GEMM=0 keeps cuBLAS + the separate GELU pass for dense -> GELU (A/B runs)
+OWN_GEMM = __import__("os").environ.get("MDT_OWN_GEMM", "1") != "0"
+
+
+def _dense_gelu(x2, w, b):
+    """``(gelu(u), u)`` with ``u = x2 @ w.T + b``: on the CTA-pair tcgen05 GEMM with the activation in its epilogue (csrc/gemm2.cu;
+    1191 vs 1543 us for cuBLAS + the GELU kernel at 238806 x 3072 x 768) when the shape qualifies, else cuBLAS + mdt_gelu_fwd."""
+    N, K = w.shape
+    if OWN_GEMM and b is not None and N % 256 == 0 and K % 64 == 0 and x2.shape[0] >= 16384 and x2.stride(1) == 1 and x2.stride(0) % 8 == 0:
+        return gemm_bias_act(x2, w, b, gelu_act=True)
+    lib = _lib.load()
+    u = torch.nn.functional.linear(x2, w, b)
+    g = torch.empty_like(u)
+    _lib.check(lib.mdt_gelu_fwd(_lib.ptr(u), _lib.ptr(g), u.shape[0], u.shape[1], _lib.stream()), "mdt_gelu_fwd")
+    return g, u
+
+
 class _PackedPostLNLayer(torch.autograd.Function):
     """x -> LN1(drop(attn(x Wqkv + b) Wo + bo) + x) = h -> LN2(drop(gelu(h W1 + b1) W2 + b2) + h) on packed rows."""
 
@@ -769,9 +784,7 @@ class _PackedPostLNLayer(torch.autograd.Function):
             att, lse = _varlen_fwd_raw(qkv, plan, p_attn, seeds[0], 64 ** -0.5)
             att = att.view(M, C)
             h, z1, mean1, rstd1 = _ln_fwd_raw(lin(att, wo, bo), x, g1, be1, p_hid, seeds[1], eps1)
-            u = lin(h, w1, b1)
-            g = torch.empty_like(u)
-            _lib.check(lib.mdt_gelu_fwd(_lib.ptr(u), _lib.ptr(g), u.shape[0], u.shape[1], _lib.stream()), "mdt_gelu_fwd")
+            g, u = _dense_gelu(h, w1, b1)
             y, z2, mean2, rstd2 = _ln_fwd_raw(lin(g, w2, b2), h, g2, be2, p_hid, seeds[2], eps2)
         ctx.save_for_backward(x, qkv, att, lse, z1, mean1, rstd1, h, u, g, z2, mean2, rstd2, wf, wo, g1, w1, w2, g2)
         ctx.plan, ctx.cfg = plan, cfg
@@ -920,9 +933,7 @@ class _VitPreLNLayer(torch.autograd.Function):
             att2 = att.reshape(Bn * T, C)
             # first residual fused with LN2: z2 = drop(o) + x is the block's inner state, h2 = LN2(z2)
             h2, z2, mean2, rstd2 = _ln_fwd_raw(lin(att2, wo, bo), x2d, g2, be2, p_hid, seeds[1], eps2)
-            u = lin(h2, w1, b1)
-            g = torch.empty_like(u)
-            _lib.check(lib.mdt_gelu_fwd(_lib.ptr(u), _lib.ptr(g), u.shape[0], u.shape[1], _lib.stream()), "mdt_gelu_fwd")
+            g, u = _dense_gelu(h2, w1, b1)
             y = _dropout_add_raw(lin(g, w2, b2), z2, p_hid, seeds[2], out_shape=(Bn, T, C))   # a base tensor, not a view:
             #                                                  the next layer rewrites its bottleneck slots in place
         ctx.save_for_backward(x2d, h1, mean1, rstd1, att2, z2, mean2, rstd2, h2, u, g, ws, wo, g1, w1, w2, g2, *actx.saved_tensors[:5])
