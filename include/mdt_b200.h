@@ -294,6 +294,12 @@ int mdt_gelu_bwd(const void *dg, const void *u, void *du, float *dbias, int64_t 
  *   bf16 row-major; lda / ldw = leading dimensions of a / w in elements; out / aux dense; N % 256 == 0, K % 64 == 0. */
 int mdt_gemm_bias_act(const void *a, int64_t lda, const void *w, int64_t ldw, const void *bias, void *out, void *aux,
                       int M, int N, int K, int act, mdt_stream_t stream);
+/* dU[M, N] = (dY[M, K] W[K, N]) * gelu'(U[M, N]): the input-gradient GEMM of the dense layer behind an exact GELU (fc2 of the
+ * feed-forward blocks, same reference lines) with the activation's derivative applied in its epilogue; W row-major [K, N] (the
+ * layer's weight as stored), bf16, N % 256 == 0, K % 64 == 0.  The bias gradient of fc1 (column sums of dU) comes out of
+ * mdt_wgrad_gemm's colsum on the same dU. */
+int mdt_gemm_dgrad_gelu(const void *dy, int64_t ldy, const void *w, int64_t ldw, const void *u, void *du, int M, int N, int K,
+                        mdt_stream_t stream);
 
 /* N2  weight gradient of a dense layer: out[N, C] += dy[M, N]^T * x[M, C]   (torch: dy.t() @ x; Hugging Face dense layers called
  *     from mDT/src/modules/multi_graphormer_fusion_layer.py:94-98,138-148, backward pass)

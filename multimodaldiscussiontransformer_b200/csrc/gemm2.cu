@@ -26,7 +26,9 @@ constexpr int kBM = 128, kBN = 256, kBK = 64, kStages = 6;   // per CTA: 128 row
 constexpr int kStageBytes = kBM * kBK * 2 + (kBN / 2) * kBK * 2;  // 32 KB
 constexpr int kOutTile = 32 * 128;                                // per epilogue warp: 32 rows x 64 bf16 columns
 constexpr int kThreads = 320;
-enum Epi : int { kEpiBias = 0, kEpiBiasGelu = 1 };
+enum Epi : int { kEpiBias = 0, kEpiBiasGelu = 1, kEpiGeluBwd = 2 };
+// kEpiGeluBwd: the input-gradient GEMM of the layer behind a GELU, dU = (dY W) * gelu'(U):  A = dY [M, K], W = [K, N] ROW-major
+// (the forward weight of that layer as it is stored; consumed MN-major, no transpose), aux = U [M, N] (read), out = dU.
 
 struct Ctrl {
     uint64_t full[kStages], empty[kStages], acc_full[2], acc_empty[2];
@@ -112,6 +114,22 @@ __device__ __forceinline__ float gelu_exact(float x) {  // x * Phi(x), Abramowit
     return x * (x >= 0.f ? 1.f - half_erfc : half_erfc);
 }
 
+// d/dx [x Phi(x)] = Phi(x) + x phi(x)
+__device__ __forceinline__ float gelu_grad(float x) {
+    const float z = fabsf(x) * 0.70710678118654752f;
+    float t, e;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, z, 1.f)));
+    float poly = fmaf(1.061405429f, t, -1.453152027f);
+    poly = fmaf(poly, t, 1.421413741f);
+    poly = fmaf(poly, t, -0.284496736f);
+    poly = fmaf(poly, t, 0.254829592f);
+    poly *= t;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-0.72134752044448170f * x * x));
+    const float half_erfc = 0.5f * poly * e;
+    const float cdf = x >= 0.f ? 1.f - half_erfc : half_erfc;
+    return fmaf(x * 0.39894228040143268f, e, cdf);
+}
+
 template <int EPI>
 __global__ void __launch_bounds__(kThreads, 1)
     gemm_pair_kernel(const __grid_constant__ CUtensorMap ma, const __grid_constant__ CUtensorMap mw, const __grid_constant__ CUtensorMap mo,
@@ -166,13 +184,18 @@ __global__ void __launch_bounds__(kThreads, 1)
                     uint8_t *st = smem + s * kStageBytes;
                     if (rank == 0) mbar_expect_tx(&ctl.full[s], 2 * kStageBytes);
                     tma_load_2d_pair(st, &ma, full_leader[s], kb * kBK, m0);
-                    tma_load_2d_pair(st + kBM * kBK * 2, &mw, full_leader[s], kb * kBK, n0);
+                    if (EPI == kEpiGeluBwd) {   // W [K, N] row-major: two boxes of [64 k-rows x 64 n-columns], consumed MN-major
+                        tma_load_2d_pair(st + kBM * kBK * 2, &mw, full_leader[s], n0, kb * kBK);
+                        tma_load_2d_pair(st + kBM * kBK * 2 + 8192, &mw, full_leader[s], n0 + 64, kb * kBK);
+                    } else {
+                        tma_load_2d_pair(st + kBM * kBK * 2, &mw, full_leader[s], kb * kBK, n0);
+                    }
                 }
             }
         }
     } else if (warp == 1) {
         if (lane == 0 && rank == 0) {
-            const uint32_t idesc = idesc_bf16(2 * kBM, kBN, 0, 0);
+            const uint32_t idesc = idesc_bf16(2 * kBM, kBN, 0, EPI == kEpiGeluBwd ? 1 : 0);
             uint32_t g = 0;
             int it = 0;
             for (int t = pair; t < n_tiles; t += n_pairs, ++it) {
@@ -186,7 +209,8 @@ __global__ void __launch_bounds__(kThreads, 1)
                     const uint32_t sa = smem_u32(smem + s * kStageBytes), sb = sa + kBM * kBK * 2;
 #pragma unroll
                     for (int k = 0; k < 4; ++k)
-                        umma_bf16_pair(tmem + acc * kBN, smem_desc_sw128(sa + k * 32, 16, 1024), smem_desc_sw128(sb + k * 32, 16, 1024),
+                        umma_bf16_pair(tmem + acc * kBN, smem_desc_sw128(sa + k * 32, 16, 1024),
+                                       EPI == kEpiGeluBwd ? smem_desc_sw128(sb + k * 2048, 8192, 1024) : smem_desc_sw128(sb + k * 32, 16, 1024),
                                        idesc, (kb > 0 || k > 0) ? 1u : 0u);
                     umma_commit_pair(&ctl.empty[s]);
                 }
@@ -215,7 +239,22 @@ __global__ void __launch_bounds__(kThreads, 1)
                 tmem_ld_32x32(lane_base + acc * kBN + half * 128 + c * 64 + 32, reinterpret_cast<uint32_t *>(v) + 32);
                 tmem_wait_ld();
                 const int n = n0 + c * 64;
-                if (a.bias != nullptr) {
+                if (EPI == kEpiGeluBwd) {   // times gelu'(u): this thread's row of U, 128 contiguous bytes (L1 keeps the line)
+                    const int m = m0 + row;
+                    if (m < a.M) {
+                        const uint4 *up = reinterpret_cast<const uint4 *>(a.aux + (size_t)m * a.N + n);
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const uint4 uw = __ldg(up + j);
+                            const uint32_t uu[4] = {uw.x, uw.y, uw.z, uw.w};
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) {
+                                v[j * 8 + 2 * e] *= gelu_grad(__uint_as_float(uu[e] << 16));
+                                v[j * 8 + 2 * e + 1] *= gelu_grad(__uint_as_float(uu[e] & 0xffff0000u));
+                            }
+                        }
+                    }
+                } else if (a.bias != nullptr) {
                     const uint4 *bp = reinterpret_cast<const uint4 *>(a.bias + n);
 #pragma unroll
                     for (int j = 0; j < 8; ++j) {
@@ -266,7 +305,6 @@ __global__ void __launch_bounds__(kThreads, 1)
             mbar_arrive_cluster(acc_empty_leader[acc]);
         }
         tma_store_wait_read();
-        (void)row;
     }
     tc_fence_before();
     __syncthreads();
@@ -288,7 +326,11 @@ int mdt_gemm_pair_launch(const void *a, int64_t lda, const void *w, int64_t ldw,
         const uint32_t box[2] = {(uint32_t)gemm2::kBK, (uint32_t)gemm2::kBM};
         if (int rc = make_tensor_map_bf16(&ma, a, 2, dims, str, box)) return rc;
     }
-    {
+    if (act == 2) {   // W [K, N] row-major
+        const uint64_t dims[2] = {(uint64_t)N, (uint64_t)K}, str[2] = {2, (uint64_t)ldw * 2};
+        const uint32_t box[2] = {64, 64};
+        if (int rc = make_tensor_map_bf16(&mw, w, 2, dims, str, box)) return rc;
+    } else {
         const uint64_t dims[2] = {(uint64_t)K, (uint64_t)N}, str[2] = {2, (uint64_t)ldw * 2};
         const uint32_t box[2] = {(uint32_t)gemm2::kBK, (uint32_t)(gemm2::kBN / 2)};
         if (int rc = make_tensor_map_bf16(&mw, w, 2, dims, str, box)) return rc;
@@ -298,7 +340,7 @@ int mdt_gemm_pair_launch(const void *a, int64_t lda, const void *w, int64_t ldw,
         const uint64_t dims[2] = {(uint64_t)N, (uint64_t)M}, str[2] = {2, (uint64_t)N * 2};
         const uint32_t box[2] = {64, 32};
         if (int rc = make_tensor_map_bf16(&mo, out, 2, dims, str, box)) return rc;
-        if (int rc = make_tensor_map_bf16(&mx, aux ? aux : out, 2, dims, str, box)) return rc;
+        if (int rc = make_tensor_map_bf16(&mx, (aux && act == 1) ? aux : out, 2, dims, str, box)) return rc;
     }
     gemm2::Args g{};
     g.M = M, g.N = N, g.K = K;
@@ -306,7 +348,8 @@ int mdt_gemm_pair_launch(const void *a, int64_t lda, const void *w, int64_t ldw,
     g.out = reinterpret_cast<__nv_bfloat16 *>(out), g.aux = reinterpret_cast<__nv_bfloat16 *>(aux);
     const int tiles = ((M + 2 * gemm2::kBM - 1) / (2 * gemm2::kBM)) * (N / gemm2::kBN);
     void (*kern)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const CUtensorMap, const gemm2::Args) =
-        act == 1 ? gemm2::gemm_pair_kernel<gemm2::kEpiBiasGelu> : gemm2::gemm_pair_kernel<gemm2::kEpiBias>;
+        act == 2 ? gemm2::gemm_pair_kernel<gemm2::kEpiGeluBwd>
+                 : (act == 1 ? gemm2::gemm_pair_kernel<gemm2::kEpiBiasGelu> : gemm2::gemm_pair_kernel<gemm2::kEpiBias>);
     MDT_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm2::kSmem));
     cudaLaunchConfig_t cfg = {};
     cudaLaunchAttribute attr[1];
@@ -331,4 +374,17 @@ int mdt_gemm_pair_launch(const void *a, int64_t lda, const void *w, int64_t ldw,
     cfg.gridDim = dim3(2 * pairs);
     MDT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mw, mo, mx, g));
     return MDT_OK;
+}
+
+// dU[M, N] = (dY[M, K] * W[K, N]) * gelu'(U[M, N]): the input-gradient GEMM of the dense layer behind an exact GELU with the
+// activation's derivative in its epilogue (no separate pass over [M, N]).  bf16; W row-major [K, N] (the layer's weight as
+// stored: out_features x in_features of the layer AFTER the activation); N % 256 == 0, K % 64 == 0.
+extern "C" int mdt_gemm_dgrad_gelu(const void *dy, int64_t ldy, const void *w, int64_t ldw, const void *u, void *du, int M, int N, int K,
+                                   mdt_stream_t stream) {
+    if (int rc = require_sm100()) return rc;
+    MDT_REQUIRE(dy && w && u && du && M >= 1, "mdt_gemm_dgrad_gelu: null pointer or M < 1");
+    MDT_REQUIRE(N % gemm2::kBN == 0 && K % gemm2::kBK == 0 && K >= gemm2::kBK, "mdt_gemm_dgrad_gelu: N must be a multiple of 256 and K of 64 (got N=%d K=%d)", N, K);
+    MDT_REQUIRE(ldy % 8 == 0 && ldw % 8 == 0 && ldy >= K && ldw >= N, "mdt_gemm_dgrad_gelu: leading dimensions must be multiples of 8, ldy >= K, ldw >= N");
+    MDT_REQUIRE((((uintptr_t)dy | (uintptr_t)w | (uintptr_t)u | (uintptr_t)du) & 15) == 0, "mdt_gemm_dgrad_gelu: buffers must be 16-byte aligned");
+    return mdt_gemm_pair_launch(dy, ldy, w, ldw, nullptr, du, const_cast<void *>(u), M, N, K, 2, as_stream(stream));
 }

@@ -770,6 +770,32 @@ def _dense_gelu(x2, w, b):
     return g, u
 
 
+def _dgrad_gelu(df, w2, u):
+    """``(du, db1 | None)`` with ``du = (df @ w2) * gelu'(u)``: on the CTA-pair GEMM with the derivative in its epilogue when the
+    shape qualifies (then the bias gradient is left to the weight-gradient kernel's column sums: ``db1 = None``), else cuBLAS +
+    ``mdt_gelu_bwd`` (which also yields ``db1``)."""
+    lib = _lib.load()
+    K, N = w2.shape
+    if (OWN_GEMM and N % 256 == 0 and K % 64 == 0 and df.shape[0] >= 16384 and df.stride(1) == 1 and df.stride(0) % 8 == 0
+            and w2.stride(1) == 1 and w2.stride(0) % 8 == 0 and u.is_contiguous()):
+        du = torch.empty_like(u)
+        _lib.check(lib.mdt_gemm_dgrad_gelu(_lib.ptr(df), df.stride(0), _lib.ptr(w2), w2.stride(0), _lib.ptr(u), _lib.ptr(du),
+                                           df.shape[0], N, K, _lib.stream()), "mdt_gemm_dgrad_gelu")
+        return du, None
+    dgl = df @ w2
+    db1 = torch.zeros(u.shape[1], dtype=torch.float32, device=u.device)
+    _lib.check(lib.mdt_gelu_bwd(_lib.ptr(dgl), _lib.ptr(u), _lib.ptr(dgl), _lib.ptr(db1), u.shape[0], u.shape[1], _lib.stream()),
+               "mdt_gelu_bwd")
+    return dgl, db1
+
+
+def _wgrad_bias(du, h, db):
+    """``(dW, db)``: the weight gradient, and the bias gradient unless the caller already has it."""
+    if db is not None:
+        return _wgrad(du, h), db
+    return _wgrad(du, h, with_colsum=True)
+
+
 class _PackedPostLNLayer(torch.autograd.Function):
     """x -> LN1(drop(attn(x Wqkv + b) Wo + bo) + x) = h -> LN2(drop(gelu(h W1 + b1) W2 + b2) + h) on packed rows."""
 
@@ -815,12 +841,9 @@ class _PackedPostLNLayer(torch.autograd.Function):
                 _move(True, tmp, t32, dy)
             # ---- feed-forward half (df may alias dh when there is no dropout: df is not read after dh is updated)
             df, dh, dg2, dbe2, db2 = _ln_bwd_raw(dy, z2, mean2, rstd2, g2, p_hid, seeds[2])
-            dw2 = df.t() @ g if need[17] else None
-            dgl = df @ w2                                              # [M, 4C]; the GELU gradient overwrites it
-            db1 = torch.zeros(u.shape[1], dtype=torch.float32, device=x.device)
-            _lib.check(lib.mdt_gelu_bwd(_lib.ptr(dgl), _lib.ptr(u), _lib.ptr(dgl), _lib.ptr(db1), u.shape[0], u.shape[1],
-                                        _lib.stream()), "mdt_gelu_bwd")
-            dw1 = _wgrad(dgl, h) if need[15] else None
+            dw2 = _wgrad(df, g) if need[17] else None
+            dgl, db1 = _dgrad_gelu(df, w2, u)                          # [M, 4C] = (df W2) * gelu'(u)
+            dw1, db1 = _wgrad_bias(dgl, h, db1)
             dh.addmm_(dgl, w1)                                         # residual gradient + input gradient: one GEMM, beta = 1
             del dgl, df
             # ---- attention half
@@ -959,12 +982,9 @@ class _VitPreLNLayer(torch.autograd.Function):
             # ---- feed-forward half: y = drop(f) + z2
             df, db2 = _dropout_bwd_raw(dy2, p_hid, seeds[2])
             dw2 = _wgrad(df, g) if need[16] else None
-            dgl = df @ w2
+            dgl, db1 = _dgrad_gelu(df, w2, u)
             del df
-            db1 = torch.zeros(u.shape[1], dtype=torch.float32, device=dy.device)
-            _lib.check(lib.mdt_gelu_bwd(_lib.ptr(dgl), _lib.ptr(u), _lib.ptr(dgl), _lib.ptr(db1), u.shape[0], u.shape[1],
-                                        _lib.stream()), "mdt_gelu_bwd")
-            dw1 = _wgrad(dgl, h2) if need[14] else None
+            dw1, db1 = _wgrad_bias(dgl, h2, db1)
             dh2 = dgl @ w1
             del dgl
             # LN2 backward; the direct path of the second residual (dy) joins d z2 inside the kernel

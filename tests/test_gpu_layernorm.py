@@ -202,3 +202,24 @@ def test_own_weight_gradient_gemm(M, N, C):
     assert float((cs.double() - want_cs).abs().max()) <= 1e-5 * max(1.0, float(want_cs.abs().max()))
     with pytest.raises(RuntimeError):
         ops.wgrad_gemm(dy[:, :200], x)                                 # N must be a multiple of 256
+
+
+@pytest.mark.parametrize("M,N,K", [(1, 256, 64), (777, 768, 256), (20000, 3072, 768), (300, 256, 3072)])
+def test_own_dgrad_gemm_with_gelu_derivative(M, N, K):
+    """``mdt_gemm_dgrad_gelu`` (CTA-pair GEMM, weight consumed MN-major): ``(dy @ w) * gelu'(u)`` against fp32 arithmetic,
+    within one bf16 rounding (<= 2^-8 relative + 1e-3)."""
+    from multimodaldiscussiontransformer_b200 import _lib
+
+    g = torch.Generator(device="cuda").manual_seed(M + N + K)
+    dy = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    w = (torch.randn(K, N, device="cuda", generator=g) * K ** -0.5).bfloat16()      # [K, N] row-major
+    u = torch.randn(M, N, device="cuda", generator=g).bfloat16()
+    du = torch.empty_like(u)
+    lib = _lib.load()
+    _lib.check(lib.mdt_gemm_dgrad_gelu(_lib.ptr(dy), dy.stride(0), _lib.ptr(w), w.stride(0), _lib.ptr(u), _lib.ptr(du), M, N, K,
+                                       _lib.stream()), "mdt_gemm_dgrad_gelu")
+    uf = u.float().requires_grad_(True)
+    torch.nn.functional.gelu(uf).backward(dy.float() @ w.float())
+    want = uf.grad
+    err = (du.float() - want).abs()
+    assert bool((err <= 2 ** -8 * want.abs() + 2e-3).all()), float(err.max())
