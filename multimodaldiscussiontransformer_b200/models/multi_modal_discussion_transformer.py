@@ -81,6 +81,7 @@ class GraphormerEncoder(FairseqEncoder):
             bert_config=getattr(args, "bert_config", None), vit_config=getattr(args, "vit_config", None))
         ge = self.graph_encoder
         self.node_encoder_stack = nn.ModuleList([ge.text_pooler, ge.text_dropout, ge.node_classifier])      # :215-221
+        ge.text_first_token_only = type(ge.text_pooler).__name__ == "BertPooler"   # the head reads hidden_states[:, 0] only
         self.share_input_output_embed = getattr(args, "share_encoder_input_output_embed", False)
         self.load_softmax = not getattr(args, "remove_head", False)
         # unused heads kept for state-dict compatibility (:231-247)

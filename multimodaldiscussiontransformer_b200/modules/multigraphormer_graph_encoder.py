@@ -96,6 +96,9 @@ class MultiGraphormerGraphEncoder(nn.Module):
             num_fusion_layers + 1, attention_dropout, activation_dropout, bert_config, vit_config)
         use_fused_layer_norms(self.vit_model)  # the trunk ViT blocks' LayerNorms on csrc/layernorm.cu as well
         use_mdt_attention(self.vit_model)      # ... and their self-attention on the tcgen05 kernels
+        #: packed text only: return [n_real, 1, 768] (token 0 of every comment, all a pooling head reads) instead of the
+        #: re-padded [n_real, 100, 768]; GraphormerEncoder switches it on, a caller that wants every token leaves it off
+        self.text_first_token_only = False
         use_fused_intermediates(self.vit_model)  # ... and dense -> GELU on csrc/gelu.cu
         use_fused_vit_layers(self.vit_model)     # ... and each block as one node (residual adds / dropouts fused)
         use_patch_gemm(self.vit_model)           # ... and the patch embedding as the GEMM it is
@@ -265,5 +268,11 @@ class MultiGraphormerGraphEncoder(nn.Module):
                 inner_states.append(x)
         x, _ = self.layers[-1](x, self_attn_padding_mask=padding_mask, self_attn_mask=attn_mask, self_attn_bias=attn_bias)
         if pack is not None:
-            bert_output = pack.unpack_text(x_text)
+            if self.text_first_token_only:
+                # the head pools token 0 of every comment (BertPooler): one row per comment instead of re-padding
+                # [n_real, 100, 768] (630 MB) forward and an index_add over 222 K rows backward
+                first = pack.cu_seqlens[:-1] + pack.nb
+                bert_output = ops.gather_rows(x_text, first.contiguous()).unsqueeze(1)
+            else:
+                bert_output = pack.unpack_text(x_text)
         return bert_output, bottle_neck, x[0, :, :]

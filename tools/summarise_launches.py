@@ -38,7 +38,7 @@ for n, v in step:
     a[0] += 1
     a[1] += v
 mine = ("mdt::", "attn_fwd_kernel", "attn_bwd_kernel", "apsp", "edges_to_adj", "node_feature", "move_rows", "attn_bias",
-        "attn_delta", "attn_dq", "mdt_", "attn::", "ln::", "gelu::", "wgrad::", "gemm::", "varlen_plan")
+        "attn_delta", "attn_dq", "mdt_", "attn::", "ln::", "gelu::", "wgrad::", "gemm::", "gemm2::", "varlen_plan")
 print(f"{'kernel':72s} {'count':>6s} {'total us':>11s} {'share':>7s} {'avg us':>9s}")
 lib = sum(t for k, (c, t) in agg.items() if "nvjet" in k or "cublas" in k or "cutlass" in k or "cudnn" in k)
 aten = sum(t for k, (c, t) in agg.items() if k.startswith("void at::") or "at_cuda_detail" in k or "elementwise_kernel_with_index" in k)
